@@ -1,0 +1,199 @@
+/* b200pt.h - C ABI of libb200pt.so, the B200 (sm_100a) path-tracing hot path.
+ *
+ * This is the drop-in boundary for ONE path of markp-gc/ipu_path_trace: the per-pixel
+ * Monte-Carlo loop of src/codelets plus the neural-image-field (NIF) environment-light
+ * MLP of src/neural_networks. The reference has no C ABI; its seam is the five string-named
+ * Poplar programs registered at src/PathTracerApp.cpp:479-483 and the StreamableTensor
+ * host<->device handles of src/ipu_utils.hpp:288-373. One entry point below replaces each.
+ * Citations are relative to the reference tree.
+ *
+ * Conventions: every function returns 0 on success and a negative b200pt_status otherwise;
+ * b200pt_last_error() gives the message. No exception crosses this boundary. A context is
+ * not thread-safe: one caller thread per context. The library owns all device memory; host
+ * pointers are never retained after a call returns. There is no CPU fallback anywhere in
+ * the library: without a CUDA device b200pt_create fails.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200pt_ctx b200pt_ctx;
+
+typedef enum b200pt_status {
+  B200PT_OK = 0,
+  B200PT_ERR_INVALID = -1,   /* bad argument / unsupported configuration */
+  B200PT_ERR_CUDA = -2,      /* a CUDA runtime call or kernel failed */
+  B200PT_ERR_STATE = -3,     /* call order violated (e.g. path_trace before upload_nif) */
+  B200PT_ERR_NOMEM = -4
+} b200pt_status;
+
+/* Byte-compatible with the reference work item, src/codelets/TraceRecord.hpp:7-19 (20 B).
+ * Items whose u >= width or v >= height are padding (LoadBalancer.cpp:66-71) and are skipped. */
+#pragma pack(push, 1)
+typedef struct b200pt_trace_record {
+  uint16_t u, v;
+  float r, g, b;
+  uint16_t sampleCount, pathLength;
+} b200pt_trace_record;
+#pragma pack(pop)
+
+enum { B200PT_AA_NORMAL = 0, B200PT_AA_UNIFORM = 1, B200PT_AA_TRUNCATED_NORMAL = 2 };
+enum { B200PT_NIF_AUTO = 0, B200PT_NIF_TCGEN05 = 1, B200PT_NIF_SIMT = 2 };
+
+/* Graph-build-time constants of the reference (IpuPathTraceJob.cpp:92-95,133-138;
+ * RuntimeConfig ipu_utils.hpp:156-165 filled at PathTracerApp.cpp:74-93). */
+typedef struct b200pt_config {
+  uint32_t struct_size;        /* = sizeof(b200pt_config) */
+  int32_t device;              /* CUDA device ordinal this context renders on */
+  uint32_t width, height;      /* full image size, -w / -h */
+  uint32_t max_path_length;    /* --max-path-length (10) */
+  uint32_t roulette_depth;     /* --roulette-depth (3); 0 is rejected (SURVEY 8a quirk ii) */
+  float stop_prob;             /* --stop-prob (0.3); rounded through binary16 like the half vertex field */
+  float refractive_index;      /* -n (1.5); rounded through binary16 */
+  int32_t aa_noise_type;       /* --aa-noise-type */
+  uint32_t max_worklist;       /* capacity in work items (pixels incl. padding) of this context */
+  uint32_t samples_per_launch; /* samples of every pixel traced per wavefront; 0 = automatic */
+  uint32_t nif_impl;           /* B200PT_NIF_* */
+} b200pt_config;
+
+/* One Dense layer as Hdf5Model hands it over (src/keras/Hdf5Model.cpp:71-82,96-133):
+ * kernel is [in,out] row-major; dtype 0 = binary16, 1 = binary32. */
+typedef struct b200pt_nif_layer {
+  int32_t in, out;
+  int32_t relu;          /* activation == "relu" (NifModel.cpp:323); "linear" -> 0 (:73-76) */
+  int32_t dtype;
+  const void* kernel;
+  const void* bias;      /* [out] or NULL */
+} b200pt_nif_layer;
+
+/* NifModel::Data + NifMetaData (NifModel.cpp:40-85, NifMetaData.cpp:11-71). */
+typedef struct b200pt_nif_desc {
+  int32_t num_layers;
+  int32_t embedding_dimension;
+  float max;             /* encode_params.max */
+  float mean[3];         /* encode_params.mean with eps already folded in (NifMetaData.cpp:48-53) */
+  int32_t log_tone_map;
+  const b200pt_nif_layer* layers;
+} b200pt_nif_desc;
+
+/* Replaces the three cycle counters of read_results (PathTracerApp.cpp:441,449,461,470-475)
+ * with device-measured times plus the path statistics the roofline needs. Totals are for the
+ * most recent b200pt_path_trace call. */
+typedef struct b200pt_counters {
+  uint64_t paths;          /* camera paths traced (valid pixels x samples) */
+  uint64_t escaped;        /* paths whose terminal record is ESCAPED = NIF evaluations */
+  uint64_t path_segments;  /* sum of path lengths ("rays", PathTracerApp.cpp:763-776) */
+  double trace_ms;         /* device time in the path-tracing kernels */
+  double nif_ms;           /* device time in the NIF kernels */
+  double total_ms;         /* device time of the whole program */
+  uint64_t kernel_launches;
+  int32_t nif_impl_used;   /* B200PT_NIF_TCGEN05 or B200PT_NIF_SIMT */
+} b200pt_counters;
+
+/* ---- lifetime -------------------------------------------------------------------------- */
+int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out);
+void b200pt_destroy(b200pt_ctx* ctx);
+/* ctx may be NULL: returns the message of the last failed b200pt_create on this thread. */
+const char* b200pt_last_error(const b200pt_ctx* ctx);
+const char* b200pt_version(void);
+
+/* ---- the five programs (PathTracerApp.cpp:479-483) ----------------------------------------- */
+
+/* "init_nif_weights" (NifModel.cpp:357-401; re-runnable mid-render, PathTracerApp.cpp:548-557). */
+int b200pt_upload_nif(b200pt_ctx* ctx, const b200pt_nif_desc* nif);
+
+/* "init_render_settings" (PathTracerApp.cpp:333-355,587-595): seed, anti-alias scale in pixels
+ * and field of view in radians (both streamed as half by the reference and rounded likewise
+ * here), HDRI azimuth in radians, on-device sample count of one path_trace program. */
+int b200pt_set_render_settings(b200pt_ctx* ctx, uint64_t seed, float aa_scale_px, float fov_rad,
+                               float azimuth_rad, uint32_t samples_per_step);
+
+/* "setup" (PathTracerApp.cpp:426,692): upload the active worklist. r,g,b,sampleCount,pathLength
+ * of the uploaded records seed the device accumulators (the reference host zeroes them). */
+int b200pt_setup(b200pt_ctx* ctx, const b200pt_trace_record* worklist, size_t n);
+
+/* "path_trace" (PathTracerApp.cpp:432-468,693): samples_per_step iterations of
+ * camera ray -> path -> escaped-ray uv -> NIF -> accumulate, with no host involvement.
+ * Asynchronous: returns once the work is enqueued; b200pt_sync waits for it.
+ * Sample indices continue from the previous call (see b200pt_set_sample_index). */
+int b200pt_path_trace(b200pt_ctx* ctx);
+int b200pt_sync(b200pt_ctx* ctx);
+
+/* "read_results" (PathTracerApp.cpp:470-475,598-603): the worklist with accumulated r,g,b,
+ * sampleCount and pathLength (the two counts wrap at 65536 exactly like the reference's
+ * uint16 fields). counters may be NULL. Implies b200pt_sync. */
+int b200pt_read_results(b200pt_ctx* ctx, b200pt_trace_record* out, size_t n, b200pt_counters* counters);
+
+/* ---- native film: replaces AccumulatedImage (src/AccumulatedImage.cpp:59-74,23-56) ----------- */
+
+/* hdr(v,u) += (b,g,r)/sampleCount for every valid work item, then clears the work-item
+ * accumulators (LoadBalancer::clearInactiveAccumulators). Device side, no transfer. */
+int b200pt_film_accumulate(b200pt_ctx* ctx);
+int b200pt_film_clear(b200pt_ctx* ctx);
+/* Copies scale * film (height x width x 3 fp32, channel order B,G,R) to a host buffer. */
+int b200pt_film_read(b200pt_ctx* ctx, float* bgr_host, float scale);
+/* Same into a device buffer on this context's device (e.g. an NCCL gather staging tensor). */
+int b200pt_film_read_device(b200pt_ctx* ctx, void* bgr_device, float scale);
+/* (hdr * scale * 2^exposure)^(1/gamma) * 255 saturated to uint8, B,G,R (AccumulatedImage.cpp:31-44). */
+int b200pt_film_tonemap(b200pt_ctx* ctx, uint8_t* bgr8_host, float scale, float exposure, float gamma);
+
+/* ---- control -------------------------------------------------------------------------- */
+int b200pt_set_sample_index(b200pt_ctx* ctx, uint32_t next_sample);
+int b200pt_get_counters(b200pt_ctx* ctx, b200pt_counters* counters);
+/* FLOPs of one NIF evaluation by the reference's own formula (NifModel.cpp:122-134). */
+int64_t b200pt_nif_flops_per_eval(const b200pt_ctx* ctx);
+
+/* ---- stage-level entry points (kernel parity tests and the NIF microbenchmark) -------------- */
+
+/* NIF inference for n (u,v) pairs -> n x 3 fp32 in the network's order B,G,R
+ * (encode NifModel.cpp:185-218, layers :299-326, decode :221-245). Host pointers. */
+int b200pt_nif_infer(b200pt_ctx* ctx, size_t n, const float* u, const float* v, float* bgr, int impl);
+/* Same on device buffers, asynchronous on the context stream; device_ms (nullable) is filled
+ * by b200pt_sync-time event timing of `repeats` back-to-back launches. */
+int b200pt_nif_infer_device(b200pt_ctx* ctx, size_t n, const void* u_dev, const void* v_dev, void* bgr_dev,
+                            int impl, int repeats, double* device_ms);
+
+/* One wavefront of sample `sample` over the uploaded worklist WITHOUT shading: per work item
+ * escaped flag, (u,v) of the env-map lookup, RGB path throughput, path length and the binary16
+ * camera ray (GenerateCameraRays codelets.cpp:36-80, RayTraceKernel :93-227,
+ * PreProcessEscapedRays :312-358). Host output arrays of n items; any may be NULL. */
+int b200pt_trace_wavefront(b200pt_ctx* ctx, uint32_t sample, size_t n, int32_t* escaped, float* uv2,
+                           float* throughput3, int32_t* length, uint16_t* cam_rays2);
+
+/* RayTraceKernel on caller-supplied inputs: n camera rays (2 binary16 each) and per_path
+ * binary16 uniforms per ray, read sequentially with wrap (codelets.cpp:147-155). Outputs as above
+ * plus the unit direction of the escaped ray. */
+int b200pt_trace_fixed(b200pt_ctx* ctx, size_t n, const uint16_t* cam_rays2, const uint16_t* uniforms,
+                       uint32_t per_path, int32_t* escaped, float* dir3, float* throughput3, int32_t* length);
+
+/* Function-level known-answer entry points; each runs the device function the path-tracing
+ * kernel itself calls. op selects the function, in/out are packed fp32 rows:
+ *   B200PT_KAT_PIXEL_TO_RAY  in [x,y,w,h,fov]            out [dx,dy,dz]     light.hpp:194-206
+ *   B200PT_KAT_SPHERE        in [o3,d3,c3,r]             out [t]            light.hpp:131-147
+ *   B200PT_KAT_DISC          in [o3,d3,n3,c3,r]          out [t]            light.hpp:106-120
+ *   B200PT_KAT_DIFFUSE       in [n3,u1,u2,rr]            out [d3,weight]    sdf.hpp:8-31
+ *   B200PT_KAT_REFLECT       in [d3,n3]                  out [d3]           sdf.hpp:36-40
+ *   B200PT_KAT_REFRACT       in [d3,n3,ri,rnd]           out [d3,refracted] sdf.hpp:45-67
+ *   B200PT_KAT_ROULETTE      in [rnd,stopProb]           out [stop,weight]  light.hpp:25-29
+ *   B200PT_KAT_ESCAPED_UV    in [d3,azimuth]             out [u,v]          codelets.cpp:333-347
+ *   B200PT_KAT_PHILOX        in 6 words as raw bits      out 4 words        (RNG shared with the oracle)
+ *   B200PT_KAT_AA_NOISE      in [w0,w1,type] raw bits    out [n0,n1]        PathTracerApp.cpp:29-45
+ *   B200PT_KAT_NIF_FEATURES  in [u,v]                    out 4E features    NifModel.cpp:185-218
+ */
+enum {
+  B200PT_KAT_PIXEL_TO_RAY = 0, B200PT_KAT_SPHERE, B200PT_KAT_DISC, B200PT_KAT_DIFFUSE, B200PT_KAT_REFLECT,
+  B200PT_KAT_REFRACT, B200PT_KAT_ROULETTE, B200PT_KAT_ESCAPED_UV, B200PT_KAT_PHILOX, B200PT_KAT_AA_NOISE,
+  B200PT_KAT_NIF_FEATURES
+};
+int b200pt_kat(b200pt_ctx* ctx, int op, size_t n, const float* in, int in_stride, float* out, int out_stride);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */

@@ -1,0 +1,147 @@
+// libb200pt C ABI (include/b200pt.h): context, the five programs of the reference
+// (PathTracerApp.cpp:479-483) and the stage-level entry points the parity tests call.
+// Host code only; kernels live in trace_kernels.cu, nif_simt.cu, nif_tc.cu, film_kernels.cu.
+#include "ctx.h"
+
+namespace {
+thread_local std::string g_createError;
+}
+
+namespace {
+
+// The hard-coded scene of the reference (codelets.cpp:110-144): five spheres and a disc, colours
+// carry the 2x gain (:127-130), no emitters (:117,142). Double-typed literals of the reference
+// (-3.23, -0.19931) narrow to float exactly as (float)literal does.
+void buildScene(SceneSoA& sc) {
+  std::memset(&sc, 0, sizeof(sc));
+  int n = 0;
+  auto sphere = [&](float cx, float cy, float cz, float r, float cr, float cg, float cb, int bsdf) {
+    sc.shape[n] = 0; sc.bsdf[n] = bsdf;
+    sc.cx[n] = cx; sc.cy[n] = cy; sc.cz[n] = cz;
+    sc.nx[n] = 0.f; sc.ny[n] = 1.f; sc.nz[n] = 0.f;
+    sc.radius2[n] = r * r; sc.planeD[n] = 0.f;
+    sc.colr[n] = cr; sc.colg[n] = cg; sc.colb[n] = cb;
+    ++n;
+  };
+  const float gain = 2.f;
+  sphere(-1.8575f, -0.98714f, -3.6f, 0.6f, 1.f * gain, .89f * gain, .55f * gain, 0);
+  sphere(0.74795f, -0.55f, -4.3816f, 1.05f, 1.f, 1.f, 1.f, 1);
+  sphere(1.9929f, -1.08666f, (float)-3.23, 0.5f, 0.75f, 0.75f, 0.75f, 2);
+  sphere((float)-0.19931, -1.183f, -2.75f, 0.4f, .8f * gain, .06f * gain, .391f * gain, 0);
+  sphere((float)-0.19931, -1.183f, -2.75f, 0.4001f, 1.f, 1.f, 1.f, 2);
+  {   // Disc(normal (0,1,0), centre (0,-1.6,-5.22), radius 3.5): ctor normalises n, d = |c.n| (light.hpp:98-101)
+    const float nx = 0.f, ny = 1.f, nz = 0.f;
+    const float inv = 1.f / std::sqrt(nx * nx + ny * ny + nz * nz);
+    const float ux = nx * inv, uy = ny * inv, uz = nz * inv;
+    const float cx = 0.f, cy = -1.6f, cz = -5.22f;
+    sc.shape[n] = 1; sc.bsdf[n] = 0;
+    sc.cx[n] = cx; sc.cy[n] = cy; sc.cz[n] = cz;
+    sc.nx[n] = ux; sc.ny[n] = uy; sc.nz[n] = uz;
+    sc.radius2[n] = 3.5f * 3.5f;
+    sc.planeD[n] = std::fabs(cx * ux + cy * uy + cz * uz);
+    sc.colr[n] = .98f * gain; sc.colg[n] = .76f * gain; sc.colb[n] = .66f * gain;
+    ++n;
+  }
+  sc.count = n;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* b200pt_version(void) { return "b200pt 0.1 (sm_100a)"; }
+
+const char* b200pt_last_error(const b200pt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_createError.c_str(); }
+
+int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
+  if (!cfg || !out) { g_createError = "null argument"; return B200PT_ERR_INVALID; }
+  *out = nullptr;
+  if (cfg->struct_size != sizeof(b200pt_config)) { g_createError = "b200pt_config.struct_size mismatch"; return B200PT_ERR_INVALID; }
+  if (cfg->width == 0 || cfg->height == 0 || cfg->width > 65535 || cfg->height > 65535) {
+    g_createError = "image size must be 1..65535 (TraceRecord coordinates are uint16)"; return B200PT_ERR_INVALID;
+  }
+  if (cfg->roulette_depth == 0) {
+    g_createError = "roulette_depth 0 makes the reference write before its record stack (codelets.cpp:176-179,219-222); rejected";
+    return B200PT_ERR_INVALID;
+  }
+  if (cfg->max_path_length == 0 || cfg->max_worklist == 0) { g_createError = "max_path_length and max_worklist must be > 0"; return B200PT_ERR_INVALID; }
+  if (cfg->aa_noise_type < 0 || cfg->aa_noise_type > 2) { g_createError = "unknown aa_noise_type"; return B200PT_ERR_INVALID; }
+  int devCount = 0;
+  cudaError_t e = cudaGetDeviceCount(&devCount);
+  if (e != cudaSuccess || devCount == 0) {
+    g_createError = std::string("no CUDA device (this library has no CPU path): ") + cudaGetErrorString(e);
+    return B200PT_ERR_CUDA;
+  }
+  if (cfg->device < 0 || cfg->device >= devCount) { g_createError = "device ordinal out of range"; return B200PT_ERR_INVALID; }
+  b200pt_ctx* c = new b200pt_ctx();
+  c->cfg = *cfg;
+  auto bail = [&](cudaError_t err, const char* what) {
+    g_createError = std::string(what) + ": " + cudaGetErrorString(err);
+    b200pt_destroy(c);
+    return B200PT_ERR_CUDA;
+  };
+  if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+  cudaDeviceProp prop{};
+  if ((e = cudaGetDeviceProperties(&prop, cfg->device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+  if (prop.major != 10) {
+    g_createError = "device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) + "; libb200pt is built for sm_100a only";
+    b200pt_destroy(c);
+    return B200PT_ERR_INVALID;
+  }
+  c->numSms = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  if ((e = cudaEventCreate(&c->evBegin)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaEventCreate(&c->evEnd)) != cudaSuccess) return bail(e, "cudaEventCreate");
+
+  const size_t cap = cfg->max_worklist;
+  uint32_t spl = cfg->samples_per_launch;
+  if (spl == 0) {
+    // automatic: enough escaped rays per wavefront to fill every SM with >= 64 tiles of 128 rows,
+    // bounded so the queue stays below ~1 GiB.
+    const size_t want = (size_t)c->numSms * 64 * 128;
+    spl = (uint32_t)std::max<size_t>(1, std::min<size_t>(32, (want + cap - 1) / cap));
+    while (spl > 1 && cap * spl * 24 > (size_t)1 << 30) --spl;
+  }
+  c->samplesPerLaunch = spl;
+  if ((e = c->recStaging.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = c->pix.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = c->sampleCount.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = c->pathLength.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = c->accum.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = c->qUv.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
+  if ((e = c->qThrSlot.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
+  if ((e = c->qCount.alloc(4)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = c->stats.alloc(4)) != cudaSuccess) return bail(e, "cudaMalloc");
+  const size_t filmN = (size_t)cfg->width * cfg->height * 3;
+  if ((e = c->film.alloc(filmN)) != cudaSuccess) return bail(e, "cudaMalloc film");
+  if ((e = c->filmOut.alloc(filmN)) != cudaSuccess) return bail(e, "cudaMalloc film");
+  if ((e = c->film8.alloc(filmN)) != cudaSuccess) return bail(e, "cudaMalloc film");
+  if ((e = cudaMemsetAsync(c->film.p, 0, filmN * sizeof(float), c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
+  if ((e = cudaMemsetAsync(c->stats.p, 0, 4 * sizeof(unsigned long long), c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
+
+  SceneSoA scene;
+  buildScene(scene);
+  if ((e = c->scene.alloc(1)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = cudaMemcpyAsync(c->scene.p, &scene, sizeof(scene), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) return bail(e, "scene upload");
+  if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+  *out = c;
+  return B200PT_OK;
+}
+
+void b200pt_destroy(b200pt_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->cfg.device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  for (cudaEvent_t e : c->evPool) cudaEventDestroy(e);
+  if (c->evBegin) cudaEventDestroy(c->evBegin);
+  if (c->evEnd) cudaEventDestroy(c->evEnd);
+  c->recStaging.release(); c->pix.release(); c->sampleCount.release(); c->pathLength.release(); c->accum.release();
+  c->qUv.release(); c->qThrSlot.release(); c->qCount.release(); c->stats.release();
+  c->scene.release(); c->film.release(); c->filmOut.release(); c->film8.release();
+  for (auto& s : c->scratch) s.release();
+  c->simtParams.release(); c->tcDev.release(); c->tcStream.release(); c->tcBias.release(); c->tcWOut.release();
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+} // extern "C"

@@ -1,0 +1,116 @@
+// Internal: the context object behind b200pt_ctx and small host helpers.
+#pragma once
+
+#include "../../include/b200pt.h"
+#include "kernels.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace b2;
+
+namespace b2host {
+
+// ---- binary16 on the host (IEEE round-to-nearest-even) -----------------------------------
+inline float hostHalfToFloat(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+inline uint16_t hostFloatToHalf(float f) { return __half_as_ushort(__float2half_rn(f)); }
+inline float hostRoundHalf(float f) { return hostHalfToFloat(hostFloatToHalf(f)); }
+
+template <class T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t alloc(size_t count) {
+    release();
+    n = count;
+    if (count == 0) return cudaSuccess;
+    return cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T));
+  }
+  cudaError_t ensure(size_t count) { return count <= n ? cudaSuccess : alloc(count); }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+} // namespace b2host
+using namespace b2host;
+
+struct b200pt_ctx {
+  b200pt_config cfg{};
+  std::string error;
+  int numSms = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t evBegin = nullptr, evEnd = nullptr;
+  std::vector<cudaEvent_t> evPool;       // per-launch timing events of the last path_trace
+  size_t evUsed = 0;
+  struct Span { size_t a, b; int kind; };  // kind 0 trace, 1 nif
+  std::vector<Span> spans;
+
+  // render settings
+  DeviceSettings settings{};
+  bool settingsSet = false;
+  uint32_t samplesPerStep = 0;
+  uint32_t nextSample = 0;
+  uint32_t samplesPerLaunch = 0;
+
+  // worklist (SoA) and accumulators
+  uint32_t nItems = 0;
+  DevBuf<TraceRecord> recStaging;
+  DevBuf<uint32_t> pix, sampleCount, pathLength;
+  DevBuf<float4> accum;
+  // wavefront queue
+  DevBuf<float2> qUv;
+  DevBuf<float4> qThrSlot;
+  DevBuf<uint32_t> qCount;
+  DevBuf<unsigned long long> stats;
+  // film
+  DevBuf<SceneSoA> scene;
+  DevBuf<float> film, filmOut;
+  DevBuf<uint8_t> film8;
+  // scratch for stage-level entry points
+  DevBuf<unsigned char> scratch[8];
+
+  // NIF
+  bool nifLoaded = false;
+  int64_t nifFlops = 0;
+  NifSimtModel simt{};
+  DevBuf<float> simtParams;
+  bool tcOk = false;
+  std::string tcWhyNot;
+  NifTcModel tcHost{};
+  DevBuf<NifTcModel> tcDev;
+  DevBuf<uint8_t> tcStream;
+  DevBuf<__half> tcBias;
+  DevBuf<float4> tcWOut;
+
+  b200pt_counters counters{};
+  bool pending = false;      // a path_trace is enqueued and not yet folded into counters
+
+  int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    error = buf;
+    return code;
+  }
+  cudaEvent_t nextEvent() {
+    if (evUsed == evPool.size()) {
+      cudaEvent_t e = nullptr;
+      if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+      evPool.push_back(e);
+    }
+    return evPool[evUsed++];
+  }
+  int cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return B200PT_OK;
+    return fail(B200PT_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  }
+};
+
+#define CU(ctx, call) do { int rc_ = (ctx)->cuda((call), #call); if (rc_) return rc_; } while (0)
+
+
+// api_nif.cu: chooses and launches the NIF kernel for `io` (impl: B200PT_NIF_*).
+int launchNif(b200pt_ctx* c, const NifIo& io, int impl, int* used);

@@ -1,0 +1,100 @@
+// Host-visible declarations of the CUDA kernels' launchers and of the device-resident
+// model descriptions. Internal to libb200pt (the public surface is include/b200pt.h).
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "pt_common.cuh"
+
+namespace b2 {
+
+// ---- path tracing (trace_kernels.cu) -----------------------------------------------------
+cudaError_t launchTraceWavefront(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
+                                 float2* qUv, float4* qThrSlot, uint32_t* qCount, uint32_t* sampleCount,
+                                 uint32_t* pathLength, unsigned long long* stats, cudaStream_t stream);
+cudaError_t launchTraceItems(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sample, int32_t* escaped, float* uv2,
+                             float* thr3, int32_t* length, uint16_t* cam2, cudaStream_t stream);
+cudaError_t launchTraceFixed(const SceneSoA* scene, const DeviceSettings& s, uint32_t n, const uint16_t* cam2, const uint16_t* uniforms, uint32_t perPath, int32_t* escaped,
+                             float* dir3, float* thr3, int32_t* length, cudaStream_t stream);
+cudaError_t launchKat(int op, uint32_t n, const float* in, int inStride, float* out, int outStride, cudaStream_t stream);
+
+// ---- NIF ---------------------------------------------------------------------------------
+constexpr int kMaxNifLayers = 16;
+constexpr int kMaxFeatures = 64;       // 4 * embedding_dimension
+
+// Where a NIF kernel reads its rows and what it does with the result.
+struct NifIo {
+  const float2* uv;          // (u,v) per row
+  const float4* thrSlot;     // path throughput rgb + work-item slot (bits); null with bgrOut
+  const uint32_t* count;     // device-resident row count (the wavefront queue length) or null
+  uint32_t countHost;        // used when count == null
+  float* bgrOut;             // n x 3 network outputs B,G,R (inference entry points) or null
+  float* accum;              // work-item accumulators, 4 floats per slot (r,g,b,unused) or null
+};
+
+// Generic description used by the SIMT kernel: fp32 copies of the binary16 parameters.
+struct NifSimtModel {
+  int numLayers, nFeat, embeddingDim, maxWidth;
+  int in[kMaxNifLayers], out[kMaxNifLayers], relu[kMaxNifLayers], hasBias[kMaxNifLayers], concat[kMaxNifLayers];
+  const float* w[kMaxNifLayers];     // [in,out] row-major
+  const float* b[kMaxNifLayers];
+  float maxv, mean[3];
+  int logToneMap;
+};
+cudaError_t launchNifSimt(const NifSimtModel& m, const NifIo& io, cudaStream_t stream);
+size_t nifSimtSmemBytes(const NifSimtModel& m);
+
+// Description used by the tcgen05 kernel: hidden layers of width H on the tensor cores,
+// the final (<= 4 outputs) layer on the CUDA cores inside the last epilogue.
+constexpr int kTcChunkKSteps = 5;     // K-steps (of 16) per weight-ring stage
+constexpr int kTcMaxChunks = 160;
+struct NifTcChunk {
+  uint32_t offset;         // byte offset into the packed weight stream
+  uint16_t bytes16;        // bytes / 16
+  uint8_t ksteps;          // MMAs in this chunk
+  uint8_t half;            // which N-half of the layer (0/1)
+  uint8_t srcFeat;         // A operand: 1 feature buffer, 0 activation buffer
+  uint8_t aKstep;          // first K-step inside the A buffer
+  uint8_t first;           // first chunk of its (layer, half): overwrite the accumulator
+  uint8_t lastOfHalf;      // last chunk of its (layer, half): accumulator complete
+  uint8_t waitAct;         // 0 none, 1 wait for activation columns [0,H/2), 2 for [H/2,H); set on the
+                           // first chunk of a layer that reads the range
+  uint8_t lastFeatUse;     // last chunk of the tile that reads the feature buffer
+  uint8_t layer;           // hidden-layer index
+  uint8_t pad;
+};
+struct NifTcModel {
+  int numHidden, H, nFeat, embeddingDim, featKSteps, numChunks;
+  int relu[kMaxNifLayers];
+  int outC, finalRelu;
+  const uint8_t* wStream;      // packed chunks (device)
+  const __half* bias;          // [numHidden][H] (device; zeros where a layer has no bias)
+  const float4* wOut;          // [H] rows of (w[k][0..3]) fp32 (device)
+  float bOut[4];
+  int finalHasBias;
+  float maxv, mean[3];
+  int logToneMap;
+  NifTcChunk chunks[kTcMaxChunks];
+};
+cudaError_t launchNifTc(const NifTcModel* modelDev, const NifTcModel& modelHost, const NifIo& io, int numSms, cudaStream_t stream);
+size_t nifTcSmemBytes(const NifTcModel& m);
+cudaError_t prepareNifTc(size_t smemBytes);
+
+// n rows of 4E binary16 features (as fp32) for the KAT entry point.
+cudaError_t launchNifFeatures(uint32_t n, const float* uvIn, int inStride, float* out, int outStride, int embeddingDim, cudaStream_t stream);
+// (u[], v[]) -> float2[]
+cudaError_t launchPackUv(uint32_t n, const float* u, const float* v, float2* uv, cudaStream_t stream);
+
+// ---- film / records (film_kernels.cu) ------------------------------------------------------
+cudaError_t launchUnpackRecords(const TraceRecord* rec, uint32_t n, uint32_t* pix, float4* accum, uint32_t* sampleCount,
+                                uint32_t* pathLength, cudaStream_t stream);
+cudaError_t launchPackRecords(TraceRecord* rec, uint32_t n, const uint32_t* pix, const float4* accum, const uint32_t* sampleCount,
+                              const uint32_t* pathLength, cudaStream_t stream);
+cudaError_t launchFilmAccumulate(uint32_t n, const uint32_t* pix, float4* accum, uint32_t* sampleCount, uint32_t* pathLength,
+                                 float* filmBgr, uint32_t width, uint32_t height, cudaStream_t stream);
+cudaError_t launchFilmScale(const float* filmBgr, float* out, size_t n, float scale, cudaStream_t stream);
+cudaError_t launchFilmTonemap(const float* filmBgr, uint8_t* out, size_t n, float scale, float exposure, float gamma, cudaStream_t stream);
+
+} // namespace b2

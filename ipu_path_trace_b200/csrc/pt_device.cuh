@@ -1,0 +1,215 @@
+// Device functions of the per-pixel Monte-Carlo loop. Each one states which reference
+// function it stands in for; none is a translation of the Poplar vertex code: the path is
+// carried forward as an RGB throughput in registers instead of the reference's 200-byte
+// per-path Contribution stack (light.hpp:263-277, codelets.cpp:235-306), and the scene is a
+// flat SoA primitive table in shared memory instead of virtual Primitive objects.
+//
+// Float operations follow the reference's order so that, with -fmad=false, every value
+// up to the libm calls (sinf/cosf/acosf/atan2f) is bit-identical to the CPU oracle.
+#pragma once
+
+#include "pt_common.cuh"
+
+namespace b2 {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 add(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 sub(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 scale(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 mul(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float norm2(V3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
+// vector.hpp:47 normalises as v * (1/sqrt(|v|^2))
+__device__ __forceinline__ V3 unit(V3 a) { return scale(a, 1.f / sqrtf(norm2(a))); }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+  return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+
+constexpr float kPi = 3.14159265358979323846264338327950288f;      // light.hpp:16
+constexpr float kEps = 1.1920928955078125e-7f;                       // FLT_EPSILON, light.cpp:5
+constexpr float kHitEps = 1e-5f;                                     // light.cpp:9
+
+// light.hpp:131-147  Sphere::intersect (geometric form)
+__device__ __forceinline__ float hitSphere(V3 centre, float radius2, V3 o, V3 d) {
+  const V3 f = sub(centre, o);
+  const float tca = dot(f, d);
+  if (tca < 0.f) return 0.f;
+  const V3 l = sub(centre, add(o, scale(d, tca)));
+  const float l2 = norm2(l);
+  if (l2 > radius2) return 0.f;
+  const float thc = sqrtf(radius2 - l2);
+  float t0 = tca - thc, t1 = tca + thc;
+  if (t0 > t1) { const float tmp = t0; t0 = t1; t1 = tmp; }
+  if (t0 < 0.f) { t0 = t1; if (t0 < 0.f) return 0.f; }
+  return t0;
+}
+
+// light.hpp:106-120  Disc::intersect
+__device__ __forceinline__ float hitDisc(V3 normal, V3 centre, float radius2, float planeD, V3 o, V3 d) {
+  const float angle = dot(normal, d);
+  if (angle != 0.f) {
+    const float t = -(dot(normal, o) + planeD) / angle;
+    if (t > kEps) {
+      const V3 hp = add(o, scale(d, t));
+      if (norm2(sub(hp, centre)) < radius2) return t;
+    }
+  }
+  return 0.f;
+}
+
+// light.hpp:173-191  Scene::intersect: closest hit with t > intersectionEpsilon; the origin is
+// advanced to the hit point and the normal evaluated there (Sphere::normal :149-151).
+__device__ __forceinline__ int closestHit(const SceneSoA& sc, V3& o, V3 d, V3& n) {
+  int best = -1;
+  float bestT = __int_as_float(0x7f800000);
+  const int count = sc.count;
+  for (int i = 0; i < count; ++i) {
+    const V3 c = v3(sc.cx[i], sc.cy[i], sc.cz[i]);
+    const float t = sc.shape[i] == 0 ? hitSphere(c, sc.radius2[i], o, d)
+                                     : hitDisc(v3(sc.nx[i], sc.ny[i], sc.nz[i]), c, sc.radius2[i], sc.planeD[i], o, d);
+    if (t > kHitEps && t < bestT) { bestT = t; best = i; }
+  }
+  if (best >= 0) {
+    o = add(o, scale(d, bestT));
+    n = sc.shape[best] == 0 ? unit(sub(o, v3(sc.cx[best], sc.cy[best], sc.cz[best])))
+                            : v3(sc.nx[best], sc.ny[best], sc.nz[best]);
+  }
+  return best;
+}
+
+// light.hpp:230-250  orthonormalSystem (first two axes; the third is the normal)
+__device__ __forceinline__ void tangentFrame(V3 n, V3& ax, V3& ay) {
+  const float nx2 = n.x * n.x, ny2 = n.y * n.y, nz2 = n.z * n.z;
+  if (fabsf(n.x) > fabsf(n.y)) {
+    const float inv = 1.f / sqrtf(nx2 + nz2);
+    ax = v3(-n.z * inv, 0.f, n.x * inv);
+  } else {
+    const float inv = 1.f / sqrtf(ny2 + nz2);
+    ax = v3(0.f, n.z * inv, -n.y * inv);
+  }
+  ay = cross(n, ax);
+}
+
+// sdf.hpp:8-31 diffuse() with hemisphere() light.hpp:223-228. Returns the record weight
+// cos(theta) * 0.1 * rr (SURVEY 8a quirk iv: not a normalised Lambert estimator; kept).
+__device__ __forceinline__ float sampleDiffuse(V3& dir, V3 n, float rr, float u1, float u2) {
+  V3 ax, ay;
+  tangentFrame(n, ax, ay);
+  const float r = sqrtf(1.f - u1 * u1);
+  const float phi = 2.f * kPi * u2;
+  const V3 h = v3(cosf(phi) * r, sinf(phi) * r, u1);
+  dir = v3(dot(v3(ax.x, ay.x, n.x), h), dot(v3(ax.y, ay.y, n.y), h), dot(v3(ax.z, ay.z, n.z), h));
+  return dot(dir, n) * .1f * rr;
+}
+
+// sdf.hpp:36-40 reflect()
+__device__ __forceinline__ void sampleMirror(V3& dir, V3 n) {
+  const float c = dot(dir, n);
+  dir = unit(sub(dir, scale(n, c * 2.f)));
+}
+
+// sdf.hpp:45-67 refract(): Schlick reflectance decides between transmission and reflection.
+__device__ __forceinline__ bool sampleGlass(V3& dir, V3 n, float ri, float rnd) {
+  float r0 = (1.f - ri) / (1.f + ri);
+  r0 = r0 * r0;
+  if (dot(n, dir) > 0.f) { n = v3(-n.x, -n.y, -n.z); } else { ri = 1.f / ri; }
+  const float c1 = -dot(n, dir);
+  const float c2 = 1.f - ri * ri * (1.f - c1 * c1);
+  const float sb = 1.f - c1;
+  const float sb2 = sb * sb;
+  const float rprob = r0 + (1.f - r0) * (sb2 * sb * sb2);
+  if (c2 > 0.f && rnd > rprob) {
+    dir = unit(add(scale(dir, ri), scale(n, ri * c1 - sqrtf(c2))));
+    return true;
+  }
+  dir = unit(add(dir, scale(n, c1 * 2.f)));
+  return false;
+}
+
+// light.hpp:194-206 pixelToRay + codelets.cpp:68-75: pixel (+ binary16 product of scale and noise)
+// -> camera-plane x,y, rounded to binary16 like the reference's half ray buffer.
+__device__ __forceinline__ void cameraRay(uint32_t pu, uint32_t pv, float noise0, float noise1,
+                                          const DeviceSettings& s, float& camX, float& camY) {
+  const float c = (float)pu + roundToHalf(s.aaScale * noise0);
+  const float r = (float)pv + roundToHalf(s.aaScale * noise1);
+  const float w = (float)s.width, h = (float)s.height;
+  const float x = (c / w) - .5f;
+  const float y = (r / h) - .5f;
+  camX = roundToHalf(2.f * x * s.aspect * s.tanHalfFov);
+  camY = roundToHalf(-2.f * y * s.tanHalfFov);
+}
+
+// codelets.cpp:333-347 PreProcessEscapedRays: direction -> equirectangular lookup (u vertical).
+// The reference evaluates atan2 in whatever precision the toolchain picks; fp32 here.
+__device__ __forceinline__ void escapedUv(V3 d, float azimuth, float& u, float& v) {
+  const float theta = acosf(d.y);
+  float phi = atan2f(d.z, d.x) + azimuth;
+  const float twoPi = 2.f * kPi;
+  if (phi < 0.f) { phi += twoPi; } else if (phi > twoPi) { phi -= twoPi; }
+  u = theta * (1.f / kPi);
+  v = phi * (1.f / twoPi);
+}
+
+struct PathResult {
+  bool escaped;
+  int length;       // records the reference would have written (END included)
+  V3 dir;           // unit direction of the escaped ray
+  V3 throughput;    // pixel += throughput (*) L_env(dir)
+};
+
+// codelets.cpp:159-223 for one camera ray. The reference pushes one Contribution per vertex
+// and folds the stack backwards afterwards (:255-298); the fold is linear in the terminal
+// colour, so the same product is carried forward here (rounding order differs: < 1e-6 rel).
+template <class Draw>
+__device__ __forceinline__ PathResult tracePath(float camX, float camY, const DeviceSettings& s,
+                                                const SceneSoA& sc, Draw&& draw) {
+  PathResult res;
+  V3 o = v3(0.f, 0.f, 0.f);
+  V3 d = unit(v3(camX, camY, -1.f));          // Ray ctor normalises (light.hpp:35)
+  V3 thr = v3(1.f, 1.f, 1.f);
+  uint32_t depth = 0;
+  int count = 0;
+  const int maxLen = (int)s.maxPathLength;
+  bool lit = false;
+  while (count != maxLen) {
+    float rr = 1.f;
+    if (depth >= s.rouletteDepth) {             // light.hpp:25-29
+      const float rnd = draw();
+      if (rnd <= s.stopProb) break;
+      rr = s.rouletteWeight;
+    }
+    V3 n;
+    const int hit = closestHit(sc, o, d, n);
+    if (hit < 0) {                              // ESCAPED record {dir, rr}
+      thr = scale(thr, rr);
+      count += 1;
+      lit = true;
+      break;
+    }
+    const int bsdf = sc.bsdf[hit];
+    if (bsdf == 0) {
+      const float u1 = draw();
+      const float u2 = draw();
+      const float w = sampleDiffuse(d, n, rr, u1, u2);
+      thr = scale(mul(thr, v3(sc.colr[hit], sc.colg[hit], sc.colb[hit])), w);
+    } else if (bsdf == 1) {
+      sampleMirror(d, n);
+      thr = scale(thr, rr);
+    } else {
+      const bool through = sampleGlass(d, n, s.refractiveIndex, draw());
+      const V3 c = through ? v3(sc.colr[hit], sc.colg[hit], sc.colb[hit]) : v3(1.f, 1.f, 1.f);
+      thr = scale(mul(thr, c), 1.15f * rr);
+    }
+    count += 1;
+    depth += 1;
+  }
+  if (!lit && count == 0) count = 1;            // END overwrites the last record (:219-222)
+  res.escaped = lit;
+  res.length = count;
+  res.dir = d;
+  res.throughput = lit ? thr : v3(0.f, 0.f, 0.f);
+  return res;
+}
+
+} // namespace b2
