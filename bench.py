@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""bench.py - path samples/s of the hot path on B200 (BASELINE.json metric, config C2/C3).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one `path_trace` program of the reference's render loop (PathTracerApp.cpp:648-776):
+samples-per-step (300) samples of every pixel of the 1104x1000 image through camera ray ->
+path -> escaped-ray NIF -> accumulate. At N > 1 (torchrun, one rank per GPU) the SAME image is
+dealt to the ranks as shuffled 16x16 pixel tiles (LoadBalancer re-read for GPUs), so total work
+is fixed: "scaling": "strong". No collective runs inside the sample loop; one NCCL reduce of the
+disjoint-support film per save interval is timed and reported separately.
+
+`value`    whole-job samples/s with the worklist resident in HBM (path_trace + film accumulate).
+`e2e`      the same through the reference-facing calls with HOST buffers every step:
+           setup (H->D worklist) + path_trace + read_results (D->H TraceRecords).
+`roofline` the NIF tcgen05 kernel: algorithmic flops (NifModel.cpp:122-134 formula x escaped rays)
+           / its CUDA-event time, against MEASURED_PEAKS.json bf16_tflops_sustained.
+`cpu_baseline` the CPU oracle (oracle/, a port: the reference has no CPU NIF) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+W, H = 1104, 1000                 # README.md:82 of the reference
+SAMPLES_PER_STEP = 300
+SAVE_INTERVAL = 10
+METRIC = "path samples/sec at 1104x1000 w/ NIF env light"
+UNIT = "samples/s"
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["bf16_tflops_sustained"]), float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json, sustained)"
+    return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device = device
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.device)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "power_w_max": float(max(power)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU legs (the only places bench.py executes oracle/)
+# ---------------------------------------------------------------------------------------------
+def cpu_sample_run(target_seconds: float, seed: int = 1):
+    """Times the CPU oracle on a bounded sample of the C2 workload: a random subset of the image's
+    16x16 pixel tiles (same dealing as the GPU sharding) at 1 sample per pixel, sized by a short
+    calibration so the whole thing takes about `target_seconds`. Returns (samples/s, description, cores)."""
+    import ipu_path_trace_b200 as pt
+    from oracle import oracle as O
+    O.build(ref=False)
+    orc = O.Oracle()
+    model = pt.synthetic_model()
+    nif = O.NifLayers(model.embedding_dimension, model.max, model.mean, model.log_tone_map, model.layers)
+    s = O.Settings(width=W, height=H, seed=seed)
+    cores = orc.num_threads()
+    tiles = pt.shard_tiles(W, H, 4313)          # one 16x16 tile per shard (69 x 63 tiles)
+    order = np.random.default_rng(7).permutation(len(tiles))
+    cal = np.concatenate([tiles[i] for i in order[:max(8, cores)]])
+    t0 = time.perf_counter()
+    orc.render(cal, 0, 1, s, nif, mode=0)
+    rate = len(cal) / (time.perf_counter() - t0)
+    n_tiles = int(min(len(tiles), max(len(cal) // 256 + 1, rate * target_seconds / 256)))
+    items = np.concatenate([tiles[i] for i in order[:n_tiles]])
+    t0 = time.perf_counter()
+    _, esc, t_tr, t_nif = orc.render(items, 0, 1, s, nif, mode=0)
+    dt = time.perf_counter() - t0
+    desc = (f"{n_tiles} random 16x16 tiles of the 1104x1000 image ({len(items)} pixels) x 1 spp, {dt:.1f} s "
+            f"(trace {t_tr:.2f} s, NIF {t_nif:.2f} s), escaped {esc / len(items):.3f}")
+    return len(items) / dt, desc, cores
+
+
+def run_reference(args) -> None:
+    """--impl reference: the reference has no CPU implementation of the NIF and its Poplar IPUModel is
+    unavailable here, so this arm times the CPU oracle: the reference's path-tracing algorithm (pinned
+    bit-for-bit against the unmodified codelets, tests/test_oracle_golden.py) + the NIF restatement, on
+    all host threads. Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    desc, cores = "", 1
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for i in range(args.warmup + args.steps):
+        v, desc, cores = cpu_sample_run(per_step)
+        if i >= args.warmup:
+            vals.append(v)
+    value = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * W * H * SAMPLES_PER_STEP / value, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32 (binary16 weights/activations, fp32 accumulate)",
+        "data": "synthetic (built-in sphere scene; seeded synthetic NIF weights in the shipped topology)",
+        "config": {"workload": f"C2: {W}x{H} spheres + NIF env light, samples-per-step {SAMPLES_PER_STEP}",
+                   "note": "each step is a bounded sample of the workload; ms_per_step is extrapolated to a full step"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args) -> None:
+    import torch
+    import ipu_path_trace_b200 as pt
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sps = args.samples_per_step
+    model = pt.synthetic_model()
+    worklist = pt.shard_tiles(W, H, world)[rank]
+    tracer = pt.PathTracer(W, H, device=local, max_worklist=len(worklist), nif_impl=pt.NIF_TCGEN05)
+    tracer.init_nif_weights(model)
+    tracer.init_render_settings(seed=1, samples_per_step=sps)
+    tracer.setup(worklist)
+    flops_per_eval = tracer.nif_flops_per_eval()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+    film_dev = torch.zeros(H * W * 3, dtype=torch.float32, device="cuda")
+
+    def step_resident():
+        tracer.path_trace(sync=False)
+        tracer.film_accumulate()
+        tracer.sync()
+
+    out_records = np.zeros(len(worklist), dtype=pt.TRACE_RECORD)
+
+    def step_e2e():
+        tracer.setup(worklist)                    # H->D TraceRecords ("setup" program)
+        tracer.path_trace(sync=False)             # "path_trace"
+        return tracer.read_results(out_records)   # D->H TraceRecords + counters ("read_results")
+
+    def gather_film():
+        """One reduce of the per-GPU films (disjoint pixel support, so the sum is a gather) to rank 0."""
+        tracer.film_read_device(film_dev.data_ptr(), 1.0)
+        if dist is not None:
+            dist.reduce(film_dev, dst=0)
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_resident()
+        flush.fill_(1)
+    barrier()
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    # ---- timed: resident ----
+    total = 0.0
+    nif_ms = trace_ms = dev_ms = 0.0
+    escaped = paths = launches = 0
+    for _ in range(args.steps):
+        flush.fill_(1)                            # L2 flush between timed iterations
+        barrier()
+        t0 = time.perf_counter()
+        step_resident()
+        barrier()
+        total += time.perf_counter() - t0
+        c = tracer.counters()
+        nif_ms += c.nif_ms; trace_ms += c.trace_ms; dev_ms += c.total_ms
+        escaped += c.escaped; paths += c.paths; launches += c.kernel_launches + 1
+    # ---- timed: end to end with host buffers ----
+    for _ in range(min(2, args.warmup)):
+        step_e2e()
+    e2e_total = 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)
+        barrier()
+        t0 = time.perf_counter()
+        step_e2e()
+        barrier()
+        e2e_total += time.perf_counter() - t0
+    # ---- the per-save-interval gather (outside the sample loop) ----
+    gather_film()
+    barrier()
+    t0 = time.perf_counter()
+    gather_film()
+    barrier()
+    gather_ms = 1e3 * (time.perf_counter() - t0)
+    clk = clocks.stop() if rank == 0 else None
+
+    stats = torch.tensor([total, e2e_total, nif_ms, trace_ms, dev_ms, gather_ms], dtype=torch.float64, device="cuda")
+    sums = torch.tensor([escaped, paths, launches], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    total, e2e_total, nif_ms, trace_ms, dev_ms, gather_ms = stats.tolist()
+    escaped, paths, launches = sums.tolist()
+
+    if rank == 0:
+        samples_per_job_step = W * H * sps
+        value = samples_per_job_step * args.steps / total
+        e2e_value = samples_per_job_step * args.steps / e2e_total
+        peak_tf, _, peak_src = measured_peaks()
+        # roofline of the dominant kernel (NIF tcgen05): algorithmic flops of the launches of one rank
+        # / the CUDA-event time of those launches on that rank's stream (max over ranks).
+        flops_rank = flops_per_eval * escaped / world
+        achieved_tf = flops_rank / (nif_ms * 1e-3) / 1e12 if nif_ms > 0 else 0.0
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f16 x f16 -> f32 (tcgen05 MLP); f32 path tracing", "data":
+            "synthetic (built-in sphere scene; seeded synthetic NIF weights in the shipped topology: converted.hdf5 is missing from the reference snapshot)",
+            "config": {"workload": f"C2: {W}x{H} spheres + NIF env light, samples-per-step {sps}, {world} GPU(s), pixel tiles 16x16 dealt round-robin",
+                       "samples_per_job_step": samples_per_job_step, "l2": "flushed (256 MiB write) between timed steps",
+                       "escaped_fraction": escaped / max(1.0, paths), "nif_flops_per_eval": flops_per_eval,
+                       "device_ms_per_step": dev_ms / args.steps, "trace_ms_per_step": trace_ms / args.steps,
+                       "nif_ms_per_step": nif_ms / args.steps, "film_gather_ms_per_save_interval": gather_ms,
+                       "save_interval_steps": SAVE_INTERVAL},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(20 * W * H), "d2h_bytes_per_step": int(20 * W * H),
+                    "ms_per_step": 1e3 * e2e_total / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
+                         "traffic": None, "kernel": "nif_tc_kernel", "peak_source": peak_src,
+                         "whole_step_frac": (flops_per_eval * escaped / world) / (dev_ms * 1e-3) / 1e12 / peak_tf if dev_ms > 0 else 0.0},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, desc, cores = cpu_sample_run(15.0)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+        print(json.dumps(line), flush=True)
+    tracer.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--samples-per-step", type=int, default=SAMPLES_PER_STEP)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    if args.gpus != world:
+        if world == 1 and args.gpus > 1:
+            # convenience: re-launch under torchrun (the driver launches torchrun itself)
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+            raise SystemExit(subprocess.call(cmd))
+        raise SystemExit(f"--gpus {args.gpus} does not match WORLD_SIZE {world}")
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

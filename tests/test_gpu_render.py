@@ -1,0 +1,130 @@
+"""End-to-end parity of the five programs (PathTracerApp.cpp:479-483) against the oracle render
+on the same Philox streams, plus size-independent properties at the BASELINE size."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rgb(items):
+    return np.stack([items["r"], items["g"], items["b"]], 1).astype(np.float64)
+
+
+def _rrmse(a, b):
+    return float(np.sqrt(np.mean((a - b) ** 2)) / np.mean(b))
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+def test_render_matches_oracle(lib_built, nif_model, O, orc, oracle_nif, impl):
+    """C1-like: 160x120 at 16 spp (oracle finishes in seconds). Same RNG counters on both sides,
+    so accumulators compare pixel by pixel; converged-image gate: relative RMSE < 1 %."""
+    W, H, spp = 160, 120, 16
+    nif_impl = lib_built.NIF_SIMT if impl == "simt" else lib_built.NIF_TCGEN05
+    t = lib_built.PathTracer(W, H, nif_impl=nif_impl)
+    t.init_nif_weights(nif_model)
+    t.init_render_settings(seed=1, samples_per_step=spp)
+    items = lib_built.create_work_list_for_image(W, H)
+    t.setup(items)
+    t.path_trace()
+    out, ctr = t.read_results()
+    want, esc, _, _ = orc.render(items, 0, spp, O.Settings(width=W, height=H), oracle_nif, mode=0)
+    assert ctr.paths == W * H * spp
+    assert abs(ctr.escaped - esc) <= 1e-3 * esc
+    assert np.all(out["sampleCount"] == spp)
+    assert abs(int(out["pathLength"].sum()) - int(want["pathLength"].sum())) <= 1e-3 * want["pathLength"].sum()
+    assert ctr.path_segments == int(out["pathLength"].sum())
+    a, b = _rgb(out), _rgb(want)
+    assert _rrmse(a, b) < 0.01
+    close = np.isclose(a, b, rtol=2e-2, atol=1e-3).all(1)
+    assert close.mean() > 0.995
+    t.close()
+
+
+def test_film_matches_accumulated_image(lib_built, nif_model):
+    """AccumulatedImage::accumulate / updateLdrImage (AccumulatedImage.cpp:59-74,23-46):
+    hdr(v,u) += (b,g,r)/sampleCount per step; ldr = (hdr*2^exposure)^(1/gamma)*255."""
+    W, H = 96, 64
+    t = lib_built.PathTracer(W, H)
+    t.init_nif_weights(nif_model)
+    t.init_render_settings(samples_per_step=4)
+    items = lib_built.create_work_list_for_image(W, H)
+    t.setup(items)
+    hdr = np.zeros((H, W, 3), np.float32)
+    steps = 3
+    for _ in range(steps):
+        t.path_trace()
+        out, _ = t.read_results()
+        hdr[out["v"], out["u"]] += np.stack([out["b"], out["g"], out["r"]], 1) / out["sampleCount"][:, None].astype(np.float32)
+        t.film_accumulate()
+        out2, _ = t.read_results()
+        assert np.all(out2["sampleCount"] == 0) and np.all(out2["r"] == 0)     # clearInactiveAccumulators
+    film = t.film_read(1.0 / steps)
+    np.testing.assert_allclose(film, hdr / steps, rtol=1e-5, atol=1e-7)
+    ldr = t.film_tonemap(1.0 / steps, exposure=0.5, gamma=2.2)
+    want = np.clip(np.power((hdr / steps) * np.float32(2.0 ** 0.5), np.float32(1 / 2.2)) * 255.0, 0, 255)
+    assert np.abs(ldr.astype(np.float32) - want).max() <= 1.01
+    t.film_clear()
+    assert np.all(t.film_read() == 0)
+    t.close()
+
+
+def test_sample_index_continues_and_is_shard_invariant(lib_built, nif_model):
+    """The image must not depend on how pixels are dealt to GPUs (RNG keyed on pixel and sample)
+    nor on how spp are split into steps."""
+    W, H = 128, 80
+    full = lib_built.create_work_list_for_image(W, H)
+
+    def render(worklists, steps, sps):
+        acc = np.zeros((H, W, 3), np.float64)
+        for wl in worklists:
+            t = lib_built.PathTracer(W, H, nif_impl=lib_built.NIF_SIMT)
+            t.init_nif_weights(nif_model)
+            t.init_render_settings(samples_per_step=sps)
+            t.setup(wl)
+            for _ in range(steps):
+                t.path_trace()
+            out, _ = t.read_results()
+            acc[out["v"], out["u"]] += _rgb(out)
+            t.close()
+        return acc
+    a = render([full], 1, 8)
+    b = render(lib_built.shard_tiles(W, H, 3), 2, 4)
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-5)
+
+
+def test_baseline_size_properties(lib_built, nif_model):
+    """C2 size (1104x1000): counts, escape statistics of SURVEY.md 8(d), finiteness, determinism of
+    the integer outputs. Oracle cannot run this size in seconds, so properties only."""
+    W, H, sps = 1104, 1000, 4
+    t = lib_built.PathTracer(W, H)
+    t.init_nif_weights(nif_model)
+    t.init_render_settings(samples_per_step=sps)
+    t.setup(lib_built.create_work_list_for_image(W, H))
+    t.path_trace()
+    out, ctr = t.read_results()
+    assert ctr.paths == W * H * sps
+    assert abs(ctr.escaped / ctr.paths - 0.9732) < 0.003
+    assert abs(ctr.path_segments / ctr.paths - 1.456) < 0.01
+    assert np.all(out["sampleCount"] == sps)
+    rgb = _rgb(out)
+    assert np.all(np.isfinite(rgb)) and rgb.min() >= 0 and rgb.mean() > 0
+    t.set_sample_index(0)
+    t.film_accumulate()
+    t.path_trace()
+    out2, ctr2 = t.read_results()
+    assert np.array_equal(out2["pathLength"], out["pathLength"]) and ctr2.escaped == ctr.escaped
+    np.testing.assert_allclose(_rgb(out2), rgb, rtol=1e-4, atol=1e-5)
+    t.close()
+
+
+def test_uint16_wrap_like_reference(lib_built, nif_model):
+    """TraceRecord.sampleCount is uint16 (TraceRecord.hpp:8-11): read_results wraps like the reference."""
+    t = lib_built.PathTracer(8, 8)
+    t.init_nif_weights(nif_model)
+    t.init_render_settings(samples_per_step=65536 + 3)
+    t.setup(lib_built.create_work_list_for_image(8, 8))
+    t.path_trace()
+    out, ctr = t.read_results()
+    assert ctr.paths == 64 * (65536 + 3)
+    assert np.all(out["sampleCount"] == 3)
+    t.close()
