@@ -98,7 +98,13 @@ __device__ __forceinline__ float sampleDiffuse(V3& dir, V3 n, float rr, float u1
   tangentFrame(n, ax, ay);
   const float r = sqrtf(1.f - u1 * u1);
   const float phi = 2.f * kPi * u2;
-  const V3 h = v3(cosf(phi) * r, sinf(phi) * r, u1);
+  // glibc's sinf/cosf (what the reference's CPU build and the oracle call) evaluate in double and
+  // round once, i.e. they are correctly rounded in all but ~1e-7 of cases; the device's sinf/cosf
+  // are 1-2 ulp. The thin clear-coat shell (radii .4 / .4001, codelets.cpp:126-131) amplifies a
+  // last-bit difference into a different hit sequence, so take the double route here as well.
+  double sd, cd;
+  sincos((double)phi, &sd, &cd);
+  const V3 h = v3((float)cd * r, (float)sd * r, u1);
   dir = v3(dot(v3(ax.x, ay.x, n.x), h), dot(v3(ax.y, ay.y, n.y), h), dot(v3(ax.z, ay.z, n.z), h));
   return dot(dir, n) * .1f * rr;
 }
@@ -141,14 +147,19 @@ __device__ __forceinline__ void cameraRay(uint32_t pu, uint32_t pv, float noise0
 }
 
 // codelets.cpp:333-347 PreProcessEscapedRays: direction -> equirectangular lookup (u vertical).
-// The reference evaluates atan2 in whatever precision the toolchain picks; fp32 here.
+// The reference calls acosf, and `atan2` unqualified on floats (codelets.cpp:334), which on a
+// glibc toolchain is the double overload: phi, the azimuth add, the wrap and the final scale run
+// in double and v is rounded to float once. The NIF encoding multiplies uv by up to 2^11 and
+// rounds to binary16 (NifModel.cpp:211-213), so a last-bit difference in uv can move a feature
+// argument by a whole binary16 step; hence the same precision choices here (acos in double
+// rounded once stands in for glibc's correctly-rounded acosf).
 __device__ __forceinline__ void escapedUv(V3 d, float azimuth, float& u, float& v) {
-  const float theta = acosf(d.y);
-  float phi = atan2f(d.z, d.x) + azimuth;
+  const float theta = (float)acos((double)d.y);
+  double phi = atan2((double)d.z, (double)d.x) + (double)azimuth;
   const float twoPi = 2.f * kPi;
-  if (phi < 0.f) { phi += twoPi; } else if (phi > twoPi) { phi -= twoPi; }
+  if (phi < 0.0) { phi += (double)twoPi; } else if (phi > (double)twoPi) { phi -= (double)twoPi; }
   u = theta * (1.f / kPi);
-  v = phi * (1.f / twoPi);
+  v = (float)(phi * (double)(1.f / twoPi));
 }
 
 struct PathResult {

@@ -228,7 +228,7 @@ __global__ void kat_kernel(int op, uint32_t n, const float* __restrict__ in, int
     case 6: {   // rouletteWeight light.hpp:25-29
       const bool stop = a[0] <= a[1];
       o[0] = stop ? 1.f : 0.f;
-      o[1] = stop ? 0.f : 1.f / (1.f - a[1]);
+      o[1] = stop ? 1.f : 1.f / (1.f - a[1]);
       break;
     }
     case 7: {   // escaped-ray uv
