@@ -7,7 +7,7 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200pt.so")
+LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(HERE, "libb200pt.so")
 
 # Every symbol include/b200pt.h declares (tests check the library exports each one).
 EXPORTS = [

@@ -5,7 +5,7 @@
 // binary16 or binary32, activation renamed to relu/none :73-76) and prepares two device forms:
 //   * fp32 copies for the general SIMT kernel (any topology);
 //   * for the shipped topology (hidden width H, optional skip-concat of the features, final layer
-//     of <= 4 outputs) the weight stream of the tcgen05 kernel: every (layer, N-half, K-range)
+//     of <= 4 outputs, padded to N = 16) the weight stream of the tcgen05 kernel: every (layer, N-half, K-range)
 //     chunk is stored as the exact shared-memory image of a K-major UMMA B operand, in MMA issue
 //     order, so the kernel's producer warp only issues linear bulk copies.
 #include "ctx.h"
@@ -121,35 +121,40 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
     std::vector<uint8_t> stream;
     int nChunks = 0;
     bool overflow = false;
-    // Appends the chunks of one (layer, half, K-range) block. kSrc0 is the first K index inside the
-    // A buffer (features or activations), rowOfK maps it to a row of the Keras kernel (-1 = zero pad).
-    auto addBlock = [&](int layer, int half, bool srcFeat, int kstepBegin, int kstepCount, auto rowOfK,
-                        bool firstOfHalf, bool lastOfHalf, int waitAct) {
+    // Appends the chunks of one (layer, N-range, K-range) block of a job. N = `nCols` output columns
+    // starting at `col0` (columns >= L.out are zero padding); kstepBegin is the first K-step inside
+    // the A buffer (features or activations), rowOfK maps a K index of that buffer to a row of the
+    // Keras kernel (-1 = zero pad).
+    auto addBlock = [&](int layer, int half, int col0, int nCols, bool srcFeat, int kstepBegin, int kstepCount, auto rowOfK,
+                        bool firstOfJob, bool lastOfJob, int waitAct, bool isOut) {
       for (int ks0 = 0; ks0 < kstepCount; ks0 += kTcChunkKSteps) {
         if (nChunks == kTcMaxChunks) { overflow = true; return; }
         const int ks = std::min(kTcChunkKSteps, kstepCount - ks0);
         NifTcChunk& ch = tm.chunks[nChunks++];
         std::memset(&ch, 0, sizeof(ch));
         ch.offset = (uint32_t)stream.size();
-        const size_t bytes = (size_t)ks * NH * 32;
+        const size_t bytes = (size_t)ks * nCols * 32;
         ch.bytes16 = (uint16_t)(bytes / 16);
-        ch.ksteps = (uint8_t)ks; ch.half = (uint8_t)half; ch.srcFeat = srcFeat ? 1 : 0;
-        ch.aKstep = (uint8_t)(kstepBegin + ks0);
-        ch.first = (firstOfHalf && ks0 == 0) ? 1 : 0;
-        ch.lastOfHalf = (lastOfHalf && ks0 + ks == kstepCount) ? 1 : 0;
+        ch.aOff16 = (uint16_t)((kstepBegin + ks0) * 4096 / 16);      // one K-step of A = 128 rows x 32 B
+        ch.ksteps = (uint8_t)ks; ch.n8 = (uint8_t)(nCols / 8);
+        ch.flags = (uint8_t)(((firstOfJob && ks0 == 0) ? kChFirst : 0) | ((lastOfJob && ks0 + ks == kstepCount) ? kChLast : 0) |
+                             (srcFeat ? kChSrcFeat : 0) | (isOut ? kChOut : 0));
         ch.waitAct = (ks0 == 0) ? (uint8_t)waitAct : 0;
-        ch.layer = (uint8_t)layer;
+        ch.layer = (uint8_t)layer; ch.half = (uint8_t)half;
         stream.resize(stream.size() + bytes, 0);
         uint16_t* dst = reinterpret_cast<uint16_t*>(stream.data() + ch.offset);
         const HostLayer& L = ls[layer];
+        // K-major UMMA B operand, no swizzle: per K-step two K-cores of [nCols rows x 8 halfs];
+        // LBO (K-core to K-core) = nCols * 16 B, SBO (8-row group to group) = 128 B.
         for (int j = 0; j < ks; ++j)
           for (int kc = 0; kc < 2; ++kc)
-            for (int nn = 0; nn < NH; ++nn)
+            for (int nn = 0; nn < nCols; ++nn)
               for (int ke = 0; ke < 8; ++ke) {
                 const int k = (kstepBegin + ks0 + j) * 16 + kc * 8 + ke;     // K index inside the A buffer
                 const int row = rowOfK(k);
-                const uint16_t v = row < 0 ? (uint16_t)0 : L.w[(size_t)row * L.out + (half * NH + nn)];
-                dst[((size_t)j * 2 + kc) * NH * 8 + (size_t)nn * 8 + ke] = v;
+                const int col = col0 + nn;
+                const uint16_t v = (row < 0 || col >= L.out) ? (uint16_t)0 : L.w[(size_t)row * L.out + col];
+                dst[((size_t)j * 2 + kc) * nCols * 8 + (size_t)nn * 8 + ke] = v;
               }
       }
     };
@@ -165,38 +170,38 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
       auto actRow = [&](int k) { return k; };
       if (usesFeat) {
         for (int half = 0; half < 2; ++half)
-          addBlock(l, half, true, 0, featKSteps, featRow, true, !usesAct, 0);
+          addBlock(l, half, half * NH, NH, true, 0, featKSteps, featRow, true, !usesAct, 0, false);
         lastFeatChunk = nChunks - 1;
       }
       if (usesAct) {
+        // K order: columns [0,H/2) for both halves, then [H/2,H) for both halves, so the layer can
+        // start as soon as the first half of the previous layer's epilogue has been written.
         for (int part = 0; part < 2; ++part)
           for (int half = 0; half < 2; ++half)
-            addBlock(l, half, false, part * halfKSteps, halfKSteps, actRow, !usesFeat && part == 0, part == 1,
-                     half == 0 ? part + 1 : 0);
+            addBlock(l, half, half * NH, NH, false, part * halfKSteps, halfKSteps, actRow, !usesFeat && part == 0, part == 1,
+                     half == 0 ? part + 1 : 0, false);
       }
+    }
+    if (!overflow) {
+      // final Dense layer (<= 4 outputs) as one N = 16 job over the last hidden activations
+      auto actRow = [&](int k) { return k; };
+      for (int part = 0; part < 2; ++part)
+        addBlock(numHidden, 0, 0, 16, false, part * halfKSteps, halfKSteps, actRow, part == 0, part == 1, part + 1, true);
     }
     if (overflow) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; }
     else {
-      tm.chunks[lastFeatChunk].lastFeatUse = 1;
+      tm.chunks[lastFeatChunk].flags |= kChLastFeatUse;
       tm.numChunks = nChunks;
       const HostLayer& last = ls.back();
       tm.outC = last.out; tm.finalRelu = last.relu; tm.finalHasBias = last.hasBias;
       std::vector<uint16_t> bias((size_t)numHidden * H, 0);
       for (int l = 0; l < numHidden; ++l) for (int i = 0; i < H; ++i) bias[(size_t)l * H + i] = ls[l].b[i];
-      std::vector<float4> wOut(H);
-      for (int k = 0; k < H; ++k) {
-        float w[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int j = 0; j < last.out; ++j) w[j] = hostHalfToFloat(last.w[(size_t)k * last.out + j]);
-        wOut[k] = make_float4(w[0], w[1], w[2], w[3]);
-      }
       for (int j = 0; j < 4; ++j) tm.bOut[j] = j < last.out ? hostHalfToFloat(last.b[j]) : 0.f;
       CU(c, c->tcStream.alloc(stream.size()));
       CU(c, cudaMemcpy(c->tcStream.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
       CU(c, c->tcBias.alloc(bias.size()));
       CU(c, cudaMemcpy(c->tcBias.p, bias.data(), bias.size() * 2, cudaMemcpyHostToDevice));
-      CU(c, c->tcWOut.alloc(wOut.size()));
-      CU(c, cudaMemcpy(c->tcWOut.p, wOut.data(), wOut.size() * sizeof(float4), cudaMemcpyHostToDevice));
-      tm.wStream = c->tcStream.p; tm.bias = c->tcBias.p; tm.wOut = c->tcWOut.p;
+      tm.wStream = c->tcStream.p; tm.bias = c->tcBias.p;
       const size_t smem = nifTcSmemBytes(tm);
       if (smem > 227 * 1024) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; }
       else {

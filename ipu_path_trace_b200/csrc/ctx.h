@@ -84,7 +84,6 @@ struct b200pt_ctx {
   DevBuf<NifTcModel> tcDev;
   DevBuf<uint8_t> tcStream;
   DevBuf<__half> tcBias;
-  DevBuf<float4> tcWOut;
 
   b200pt_counters counters{};
   bool pending = false;      // a path_trace is enqueued and not yet folded into counters

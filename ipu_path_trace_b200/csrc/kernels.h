@@ -46,32 +46,31 @@ struct NifSimtModel {
 cudaError_t launchNifSimt(const NifSimtModel& m, const NifIo& io, cudaStream_t stream);
 size_t nifSimtSmemBytes(const NifSimtModel& m);
 
-// Description used by the tcgen05 kernel: hidden layers of width H on the tensor cores,
-// the final (<= 4 outputs) layer on the CUDA cores inside the last epilogue.
+// Description used by the tcgen05 kernel: every Dense layer on the tensor cores. A hidden layer's
+// N = H outputs are computed as two half "jobs" (N = H/2 each, own TMEM accumulator); the final
+// layer (<= 4 outputs) is one job padded to N = 16.
 constexpr int kTcChunkKSteps = 5;     // K-steps (of 16) per weight-ring stage
 constexpr int kTcMaxChunks = 160;
-struct NifTcChunk {
+enum : uint8_t { kChFirst = 1, kChLast = 2, kChSrcFeat = 4, kChLastFeatUse = 8, kChOut = 16 };
+struct NifTcChunk {        // 16 bytes, read as one uint4 by the MMA thread
   uint32_t offset;         // byte offset into the packed weight stream
   uint16_t bytes16;        // bytes / 16
+  uint16_t aOff16;         // byte offset / 16 of the first K-step inside the A buffer
   uint8_t ksteps;          // MMAs in this chunk
-  uint8_t half;            // which N-half of the layer (0/1)
-  uint8_t srcFeat;         // A operand: 1 feature buffer, 0 activation buffer
-  uint8_t aKstep;          // first K-step inside the A buffer
-  uint8_t first;           // first chunk of its (layer, half): overwrite the accumulator
-  uint8_t lastOfHalf;      // last chunk of its (layer, half): accumulator complete
-  uint8_t waitAct;         // 0 none, 1 wait for activation columns [0,H/2), 2 for [H/2,H); set on the
+  uint8_t n8;              // N / 8 of those MMAs
+  uint8_t flags;           // kCh*: first / last chunk of its job, A operand = feature buffer,
+                           // last reader of the feature buffer in the tile, output-layer job
+  uint8_t waitAct;         // 0 none, 1 wait for activation columns [0,H/2), 2 for [H/2,H): set on the
                            // first chunk of a layer that reads the range
-  uint8_t lastFeatUse;     // last chunk of the tile that reads the feature buffer
-  uint8_t layer;           // hidden-layer index
-  uint8_t pad;
+  uint8_t layer, half, pad0, pad1;
 };
+static_assert(sizeof(NifTcChunk) == 16, "chunk table entries are loaded as uint4");
 struct NifTcModel {
   int numHidden, H, nFeat, embeddingDim, featKSteps, numChunks;
   int relu[kMaxNifLayers];
   int outC, finalRelu;
   const uint8_t* wStream;      // packed chunks (device)
   const __half* bias;          // [numHidden][H] (device; zeros where a layer has no bias)
-  const float4* wOut;          // [H] rows of (w[k][0..3]) fp32 (device)
   float bOut[4];
   int finalHasBias;
   float maxv, mean[3];
