@@ -36,6 +36,99 @@ std::string tcEligibility(const std::vector<HostLayer>& ls, int nFeat) {
   return "";
 }
 
+// Builds the tcgen05 kernel's model: the chunk table and the packed weight stream. Every (layer,
+// N-range, K-range) chunk is the exact shared-memory image of a K-major UMMA B operand, in MMA issue
+// order; for a CTA pair (cg == 2) a chunk is stored as [image of CTA 0's N/2 rows | image of CTA 1's].
+bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200pt_nif_desc& nif, int cg, NifTcModel& tm,
+                  std::vector<uint8_t>& stream) {
+  std::memset(&tm, 0, sizeof(tm));
+  const int numHidden = (int)ls.size() - 1;
+  const int H = ls[0].out, NH = H / 2;
+  const int featKSteps = (nFeat + 15) / 16;
+  const int halfKSteps = NH / 16;
+  tm.numHidden = numHidden; tm.H = H; tm.nFeat = nFeat; tm.embeddingDim = E; tm.featKSteps = featKSteps;
+  tm.maxv = nif.max; tm.mean[0] = nif.mean[0]; tm.mean[1] = nif.mean[1]; tm.mean[2] = nif.mean[2];
+  tm.logToneMap = nif.log_tone_map ? 1 : 0;
+  int nChunks = 0;
+  bool overflow = false;
+  // Appends the chunks of one (layer, N-range, K-range) block of a job. N = `nCols` output columns
+  // starting at `col0` (columns >= L.out are zero padding); kstepBegin is the first K-step inside
+  // the A buffer (features or activations), rowOfK maps a K index of that buffer to a row of the
+  // Keras kernel (-1 = zero pad).
+  auto addBlock = [&](int layer, int half, int col0, int nCols, bool srcFeat, int kstepBegin, int kstepCount, auto rowOfK,
+                      bool firstOfJob, bool lastOfJob, int waitAct, bool isOut) {
+    for (int ks0 = 0; ks0 < kstepCount; ks0 += kTcChunkKSteps) {
+      if (nChunks == kTcMaxChunks) { overflow = true; return; }
+      const int ks = std::min(kTcChunkKSteps, kstepCount - ks0);
+      NifTcChunk& ch = tm.chunks[nChunks++];
+      std::memset(&ch, 0, sizeof(ch));
+      ch.offset = (uint32_t)stream.size();
+      const size_t bytes = (size_t)ks * nCols * 32;
+      ch.bytes16 = (uint16_t)(bytes / 16);
+      ch.aOff16 = (uint16_t)((kstepBegin + ks0) * 4096 / 16);      // one K-step of A = 128 rows x 32 B
+      ch.ksteps = (uint8_t)ks; ch.n8 = (uint8_t)(nCols / 8);
+      ch.flags = (uint8_t)(((firstOfJob && ks0 == 0) ? kChFirst : 0) | ((lastOfJob && ks0 + ks == kstepCount) ? kChLast : 0) |
+                           (srcFeat ? kChSrcFeat : 0) | (isOut ? kChOut : 0));
+      ch.waitAct = (ks0 == 0) ? (uint8_t)waitAct : 0;
+      ch.layer = (uint8_t)layer; ch.half = (uint8_t)half;
+      stream.resize(stream.size() + bytes, 0);
+      uint16_t* dst = reinterpret_cast<uint16_t*>(stream.data() + ch.offset);
+      const HostLayer& L = ls[layer];
+      // K-major UMMA B operand, no swizzle: per K-step two K-cores of [rows x 8 halfs];
+      // LBO (K-core to K-core) = rows * 16 B, SBO (8-row group to group) = 128 B.
+      const int rows = nCols / cg;                                  // B rows (output columns) held by one CTA
+      for (int rk = 0; rk < cg; ++rk)
+        for (int j = 0; j < ks; ++j)
+          for (int kc = 0; kc < 2; ++kc)
+            for (int nn = 0; nn < rows; ++nn)
+              for (int ke = 0; ke < 8; ++ke) {
+                const int k = (kstepBegin + ks0 + j) * 16 + kc * 8 + ke;     // K index inside the A buffer
+                const int row = rowOfK(k);
+                const int col = col0 + rk * rows + nn;
+                const uint16_t v = (row < 0 || col >= L.out) ? (uint16_t)0 : L.w[(size_t)row * L.out + col];
+                dst[(size_t)rk * ks * rows * 16 + ((size_t)j * 2 + kc) * rows * 8 + (size_t)nn * 8 + ke] = v;
+              }
+    }
+  };
+  int lastFeatChunk = -1;
+  for (int l = 0; l < numHidden && !overflow; ++l) {
+    const HostLayer& L = ls[l];
+    const bool usesAct = (l > 0);
+    const bool usesFeat = (l == 0) || (L.in == H + nFeat);
+    tm.relu[l] = L.relu;
+    // concat order is [activations, features] (NifModel.cpp:305): feature k -> kernel row H + k
+    const int featRow0 = usesAct ? H : 0;
+    auto featRow = [&](int k) { return k < nFeat ? featRow0 + k : -1; };
+    auto actRow = [&](int k) { return k; };
+    if (usesFeat) {
+      for (int half = 0; half < 2; ++half)
+        addBlock(l, half, half * NH, NH, true, 0, featKSteps, featRow, true, !usesAct, 0, false);
+      lastFeatChunk = nChunks - 1;
+    }
+    if (usesAct) {
+      // K order: columns [0,H/2) for both halves, then [H/2,H) for both halves, so the layer can
+      // start as soon as the first half of the previous layer's epilogue has been written.
+      for (int part = 0; part < 2; ++part)
+        for (int half = 0; half < 2; ++half)
+          addBlock(l, half, half * NH, NH, false, part * halfKSteps, halfKSteps, actRow, !usesFeat && part == 0, part == 1,
+                   half == 0 ? part + 1 : 0, false);
+    }
+  }
+  if (!overflow) {
+    // final Dense layer (<= 4 outputs) as one N = 16 job over the last hidden activations
+    auto actRow = [&](int k) { return k; };
+    for (int part = 0; part < 2; ++part)
+      addBlock(numHidden, 0, 0, 16, false, part * halfKSteps, halfKSteps, actRow, part == 0, part == 1, part + 1, true);
+  }
+  if (overflow) return false;
+  tm.chunks[lastFeatChunk].flags |= kChLastFeatUse;
+  tm.numChunks = nChunks;
+  const HostLayer& last = ls.back();
+  tm.outC = last.out; tm.finalRelu = last.relu; tm.finalHasBias = last.hasBias;
+  for (int j = 0; j < 4; ++j) tm.bOut[j] = j < last.out ? hostHalfToFloat(last.b[j]) : 0.f;
+  return true;
+}
+
 } // namespace
 
 extern "C" {
@@ -108,107 +201,30 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
   c->tcWhyNot = tcEligibility(ls, nFeat);
   c->tcOk = c->tcWhyNot.empty();
   if (c->tcOk) {
-    NifTcModel& tm = c->tcHost;
-    std::memset(&tm, 0, sizeof(tm));
     const int numHidden = (int)ls.size() - 1;
-    const int H = ls[0].out, NH = H / 2;
-    const int featKSteps = (nFeat + 15) / 16;
-    const int halfKSteps = NH / 16;
-    tm.numHidden = numHidden; tm.H = H; tm.nFeat = nFeat; tm.embeddingDim = E; tm.featKSteps = featKSteps;
-    tm.maxv = nif->max; tm.mean[0] = nif->mean[0]; tm.mean[1] = nif->mean[1]; tm.mean[2] = nif->mean[2];
-    tm.logToneMap = nif->log_tone_map ? 1 : 0;
-
-    std::vector<uint8_t> stream;
-    int nChunks = 0;
-    bool overflow = false;
-    // Appends the chunks of one (layer, N-range, K-range) block of a job. N = `nCols` output columns
-    // starting at `col0` (columns >= L.out are zero padding); kstepBegin is the first K-step inside
-    // the A buffer (features or activations), rowOfK maps a K index of that buffer to a row of the
-    // Keras kernel (-1 = zero pad).
-    auto addBlock = [&](int layer, int half, int col0, int nCols, bool srcFeat, int kstepBegin, int kstepCount, auto rowOfK,
-                        bool firstOfJob, bool lastOfJob, int waitAct, bool isOut) {
-      for (int ks0 = 0; ks0 < kstepCount; ks0 += kTcChunkKSteps) {
-        if (nChunks == kTcMaxChunks) { overflow = true; return; }
-        const int ks = std::min(kTcChunkKSteps, kstepCount - ks0);
-        NifTcChunk& ch = tm.chunks[nChunks++];
-        std::memset(&ch, 0, sizeof(ch));
-        ch.offset = (uint32_t)stream.size();
-        const size_t bytes = (size_t)ks * nCols * 32;
-        ch.bytes16 = (uint16_t)(bytes / 16);
-        ch.aOff16 = (uint16_t)((kstepBegin + ks0) * 4096 / 16);      // one K-step of A = 128 rows x 32 B
-        ch.ksteps = (uint8_t)ks; ch.n8 = (uint8_t)(nCols / 8);
-        ch.flags = (uint8_t)(((firstOfJob && ks0 == 0) ? kChFirst : 0) | ((lastOfJob && ks0 + ks == kstepCount) ? kChLast : 0) |
-                             (srcFeat ? kChSrcFeat : 0) | (isOut ? kChOut : 0));
-        ch.waitAct = (ks0 == 0) ? (uint8_t)waitAct : 0;
-        ch.layer = (uint8_t)layer; ch.half = (uint8_t)half;
-        stream.resize(stream.size() + bytes, 0);
-        uint16_t* dst = reinterpret_cast<uint16_t*>(stream.data() + ch.offset);
-        const HostLayer& L = ls[layer];
-        // K-major UMMA B operand, no swizzle: per K-step two K-cores of [nCols rows x 8 halfs];
-        // LBO (K-core to K-core) = nCols * 16 B, SBO (8-row group to group) = 128 B.
-        for (int j = 0; j < ks; ++j)
-          for (int kc = 0; kc < 2; ++kc)
-            for (int nn = 0; nn < nCols; ++nn)
-              for (int ke = 0; ke < 8; ++ke) {
-                const int k = (kstepBegin + ks0 + j) * 16 + kc * 8 + ke;     // K index inside the A buffer
-                const int row = rowOfK(k);
-                const int col = col0 + nn;
-                const uint16_t v = (row < 0 || col >= L.out) ? (uint16_t)0 : L.w[(size_t)row * L.out + col];
-                dst[((size_t)j * 2 + kc) * nCols * 8 + (size_t)nn * 8 + ke] = v;
-              }
-      }
-    };
-    int lastFeatChunk = -1;
-    for (int l = 0; l < numHidden && !overflow; ++l) {
-      const HostLayer& L = ls[l];
-      const bool usesAct = (l > 0);
-      const bool usesFeat = (l == 0) || (L.in == H + nFeat);
-      tm.relu[l] = L.relu;
-      // concat order is [activations, features] (NifModel.cpp:305): feature k -> kernel row H + k
-      const int featRow0 = usesAct ? H : 0;
-      auto featRow = [&](int k) { return k < nFeat ? featRow0 + k : -1; };
-      auto actRow = [&](int k) { return k; };
-      if (usesFeat) {
-        for (int half = 0; half < 2; ++half)
-          addBlock(l, half, half * NH, NH, true, 0, featKSteps, featRow, true, !usesAct, 0, false);
-        lastFeatChunk = nChunks - 1;
-      }
-      if (usesAct) {
-        // K order: columns [0,H/2) for both halves, then [H/2,H) for both halves, so the layer can
-        // start as soon as the first half of the previous layer's epilogue has been written.
-        for (int part = 0; part < 2; ++part)
-          for (int half = 0; half < 2; ++half)
-            addBlock(l, half, half * NH, NH, false, part * halfKSteps, halfKSteps, actRow, !usesFeat && part == 0, part == 1,
-                     half == 0 ? part + 1 : 0, false);
-      }
+    const int H = ls[0].out;
+    std::vector<uint16_t> bias((size_t)numHidden * H, 0);
+    for (int l = 0; l < numHidden; ++l) for (int i = 0; i < H; ++i) bias[(size_t)l * H + i] = ls[l].b[i];
+    CU(c, c->tcBias.alloc(bias.size()));
+    CU(c, cudaMemcpy(c->tcBias.p, bias.data(), bias.size() * 2, cudaMemcpyHostToDevice));
+    for (int cg = 1; cg <= 2 && c->tcOk; ++cg) {
+      NifTcModel& tm = c->tcHost[cg - 1];
+      std::vector<uint8_t> stream;
+      if (!buildTcModel(ls, nFeat, E, *nif, cg, tm, stream)) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; break; }
+      DevBuf<uint8_t>& dev = c->tcStream[cg - 1];
+      CU(c, dev.alloc(stream.size()));
+      CU(c, cudaMemcpy(dev.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
+      tm.wStream = dev.p; tm.bias = c->tcBias.p;
+      const size_t smem = nifTcSmemBytes(tm, cg);
+      if (smem > 227 * 1024) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; break; }
+      CU(c, prepareNifTc(smem, cg));
     }
-    if (!overflow) {
-      // final Dense layer (<= 4 outputs) as one N = 16 job over the last hidden activations
-      auto actRow = [&](int k) { return k; };
-      for (int part = 0; part < 2; ++part)
-        addBlock(numHidden, 0, 0, 16, false, part * halfKSteps, halfKSteps, actRow, part == 0, part == 1, part + 1, true);
-    }
-    if (overflow) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; }
-    else {
-      tm.chunks[lastFeatChunk].flags |= kChLastFeatUse;
-      tm.numChunks = nChunks;
-      const HostLayer& last = ls.back();
-      tm.outC = last.out; tm.finalRelu = last.relu; tm.finalHasBias = last.hasBias;
-      std::vector<uint16_t> bias((size_t)numHidden * H, 0);
-      for (int l = 0; l < numHidden; ++l) for (int i = 0; i < H; ++i) bias[(size_t)l * H + i] = ls[l].b[i];
-      for (int j = 0; j < 4; ++j) tm.bOut[j] = j < last.out ? hostHalfToFloat(last.b[j]) : 0.f;
-      CU(c, c->tcStream.alloc(stream.size()));
-      CU(c, cudaMemcpy(c->tcStream.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
-      CU(c, c->tcBias.alloc(bias.size()));
-      CU(c, cudaMemcpy(c->tcBias.p, bias.data(), bias.size() * 2, cudaMemcpyHostToDevice));
-      tm.wStream = c->tcStream.p; tm.bias = c->tcBias.p;
-      const size_t smem = nifTcSmemBytes(tm);
-      if (smem > 227 * 1024) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; }
-      else {
-        CU(c, prepareNifTc(smem));
-        CU(c, c->tcDev.alloc(1));
-        CU(c, cudaMemcpy(c->tcDev.p, &tm, sizeof(tm), cudaMemcpyHostToDevice));
-      }
+    if (c->tcOk) {
+      // CTA pairs (cta_group::2) halve the L2 -> SM weight traffic per row; use them when every SM can
+      // be part of a resident pair. B200PT_NIF_CG=1|2 overrides (A/B measurements).
+      c->tcMaxPairs = nifTcMaxPairs(c->tcHost[1]);
+      c->tcCg = 1;   // measured (profiles/): pairs are not yet faster than single CTAs; B200PT_NIF_CG=2 selects them
+      if (const char* e = getenv("B200PT_NIF_CG")) { if (e[0] == '1') c->tcCg = 1; else if (e[0] == '2' && c->tcMaxPairs > 0) c->tcCg = 2; }
     }
   }
   if (c->cfg.nif_impl == B200PT_NIF_TCGEN05 && !c->tcOk)
@@ -229,7 +245,7 @@ int launchNif(b200pt_ctx* c, const NifIo& io, int impl, int* used) {
   if (impl == B200PT_NIF_AUTO) impl = c->tcOk ? B200PT_NIF_TCGEN05 : B200PT_NIF_SIMT;
   if (impl == B200PT_NIF_TCGEN05) {
     if (!c->tcOk) return c->fail(B200PT_ERR_INVALID, "tcgen05 NIF path unavailable for this model: %s", c->tcWhyNot.c_str());
-    CU(c, launchNifTc(c->tcDev.p, c->tcHost, io, c->numSms, c->stream));
+    CU(c, launchNifTc(c->tcHost[c->tcCg - 1], io, c->tcCg, c->numSms, c->tcMaxPairs, c->stream));
   } else if (impl == B200PT_NIF_SIMT) {
     CU(c, launchNifSimt(c->simt, io, c->stream));
   } else {

@@ -77,9 +77,11 @@ struct NifTcModel {
   int logToneMap;
   NifTcChunk chunks[kTcMaxChunks];
 };
-cudaError_t launchNifTc(const NifTcModel* modelDev, const NifTcModel& modelHost, const NifIo& io, int numSms, cudaStream_t stream);
-size_t nifTcSmemBytes(const NifTcModel& m);
-cudaError_t prepareNifTc(size_t smemBytes);
+// cg = CTAs per MMA group: 1, or 2 = CTA pairs (cluster of 2, tcgen05 cta_group::2)
+cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int cg, int numSms, int maxPairs, cudaStream_t stream);
+size_t nifTcSmemBytes(const NifTcModel& m, int cg);
+cudaError_t prepareNifTc(size_t smemBytes, int cg);
+int nifTcMaxPairs(const NifTcModel& m);
 
 // n rows of 4E binary16 features (as fp32) for the KAT entry point.
 cudaError_t launchNifFeatures(uint32_t n, const float* uvIn, int inStride, float* out, int outStride, int embeddingDim, cudaStream_t stream);

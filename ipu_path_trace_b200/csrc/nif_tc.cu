@@ -27,36 +27,49 @@
 namespace b2 {
 
 constexpr int kTcRows = 128;
-constexpr int kTcStages = 4;
 constexpr int kEncodeWarps = 4;
 constexpr int kEpiWarps = 8;
 constexpr int kTcThreads = 32 * (2 + kEncodeWarps + kEpiWarps);
-constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kFirstEncodeWarp = 2;
 constexpr int kFirstEpiWarp = 2 + kEncodeWarps;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kOutTmemCol = 480;      // the N=16 output accumulator sits after the three H/2 <= 160 column slots
+// weight-ring depth: the CTA pair holds half a chunk per CTA, so the same bytes give twice the stages
+
 
 // ---- PTX wrappers ------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
+__device__ __forceinline__ uint32_t clusterCtaRank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void clusterSync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address of this CTA -> shared::cluster address of the same offset in CTA `rank`
+__device__ __forceinline__ uint32_t mapToCta(uint32_t addr, uint32_t rank) {
+  uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
+}
 __device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
 __device__ __forceinline__ void mbarArrive(uint32_t bar) {
   asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(bar) : "memory");
 }
+// arrive on a barrier of another (or this) CTA of the cluster, given its shared::cluster address
+__device__ __forceinline__ void mbarArriveCluster(uint32_t clusterAddr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(clusterAddr) : "memory");
+}
 __device__ __forceinline__ void mbarArriveExpectTx(uint32_t bar, uint32_t bytes) {
   asm volatile("{ .reg .b64 st; mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1; }" ::"r"(bar), "r"(bytes) : "memory");
 }
 // Bounded wait: a protocol bug traps (CUDA error at the API) instead of hanging the GPU.
 // try_wait itself blocks for a hardware-defined time slice, so the spin count stays small.
+template <int CG>
 __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   uint32_t spins = 0;
   while (true) {
     asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+                   : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     if (done) break;
     if (++spins > (1u << 26)) __trap();
   }
@@ -69,16 +82,32 @@ __device__ __forceinline__ void fenceProxyAsync() { asm volatile("fence.proxy.as
 __device__ __forceinline__ void fenceBarrierInit() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void tcFenceBefore() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcFenceAfter() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// MMA-completion arrive. CG == 2: the arrive is multicast to the barrier at this offset in both CTAs.
+template <int CG>
 __device__ __forceinline__ void tcCommit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+  if (CG == 2)
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+  else
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // D[tmem] (+)= A[smem desc] * B[smem desc]; descriptors passed as (lo, hi) 32-bit halves.
+// CG == 2: one instruction drives the tensor cores of both SMs of the pair (M = 256): each CTA
+// supplies its own 128 rows of A and half of the N columns of B from the same smem offsets.
+template <int CG>
 __device__ __forceinline__ void tcMma(uint32_t dTmem, uint32_t aLo, uint32_t bLo, uint32_t descHi, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
-      "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
-      ::"r"(dTmem), "r"(aLo), "r"(bLo), "r"(descHi), "r"(idesc), "r"(accumulate) : "memory");
+  if (CG == 2)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(dTmem), "r"(aLo), "r"(bLo), "r"(descHi), "r"(idesc), "r"(accumulate) : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(dTmem), "r"(aLo), "r"(bLo), "r"(descHi), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tcLoad16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
@@ -99,8 +128,9 @@ __device__ __forceinline__ void tcWaitLoad() { asm volatile("tcgen05.wait::ld.sy
 // core matrices of one K=16 step, SBO (= 128 B here) the distance between consecutive 8-row
 // groups. lo = start address >> 4 | (LBO >> 4) << 16; hi = SBO >> 4 | version 1 at bit 46.
 constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
-// Instruction descriptor (cute::UMMA::InstrDescriptor): fp16 x fp16 -> fp32, both K-major, M = 128.
-__device__ __forceinline__ uint32_t umInstr(uint32_t n8) { return (1u << 4) | (n8 << 17) | ((uint32_t)(kTcRows >> 4) << 24); }
+// Instruction descriptor (cute::UMMA::InstrDescriptor): fp16 x fp16 -> fp32, both K-major, M = 128 per CTA.
+template <int CG>
+__device__ __forceinline__ uint32_t umInstr(uint32_t n8) { return (1u << 4) | (n8 << 17) | ((uint32_t)((kTcRows * CG) >> 4) << 24); }
 
 // Optional in-kernel timers (build with -DB200PT_PROFILE; scratch/nif_prof.py reads them).
 #ifdef B200PT_PROFILE
@@ -109,33 +139,40 @@ __device__ unsigned long long g_tcProf[148 * 16];
 #define PROF_ADD(var, t0) (var) += clock64() - (t0)
 #else
 #define PROF_T() 0ll
-#define PROF_ADD(var, t0) ((void)(t0))
+#define PROF_ADD(var, t0) ((void)(var), (void)(t0))
 #endif
 
 struct TcSmem {
   // byte offsets from the dynamic shared memory base
-  uint32_t act, feat[2], ring, bias, chunks, bars, tmemSlot, total;
+  uint32_t act, feat[2], ring, bias, bars, tmemSlot, total;
 };
-__host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden, int numChunks) {
+// cg = CTAs per MMA group (1, or 2 for a CTA pair): the ring holds 1/cg of every chunk per CTA.
+__host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden, int cg) {
   TcSmem s;
   uint32_t o = 0;
   s.act = o; o += (uint32_t)H * kTcRows * 2;
   s.feat[0] = o; o += (uint32_t)featKSteps * 4096;
   s.feat[1] = o; o += (uint32_t)featKSteps * 4096;
-  s.ring = o; o += (uint32_t)kTcStages * kTcChunkKSteps * (uint32_t)(H / 2) * 32;
+  s.ring = o; o += (uint32_t)(cg == 2 ? 8 : 4) * kTcChunkKSteps * (uint32_t)(H / 2 / cg) * 32;
   s.bias = o; o += (uint32_t)numHidden * H * 2;
-  s.chunks = o; o += (uint32_t)numChunks * (uint32_t)sizeof(NifTcChunk);
   o = (o + 15u) & ~15u;
-  s.bars = o; o += 32 * 8;
+  s.bars = o; o += 48 * 8;
   s.tmemSlot = o; o += 16;
   s.total = o;
   return s;
 }
 
 // barrier indices inside the bars block
-enum { BAR_W_FULL = 0, BAR_W_EMPTY = 4, BAR_FEAT_FULL = 8, BAR_FEAT_EMPTY = 10,
-       BAR_ACC_FULL = 12, BAR_ACC_EMPTY = 15, BAR_ACT_READY = 18, BAR_OUT_FULL = 20, BAR_OUT_EMPTY = 21, BAR_COUNT = 22 };
+enum { BAR_W_FULL = 0, BAR_W_EMPTY = 8, BAR_PEER_W_FULL = 16, BAR_FEAT_FULL = 24, BAR_FEAT_EMPTY = 26,
+       BAR_ACC_FULL = 28, BAR_ACC_EMPTY = 31, BAR_ACT_READY = 34, BAR_OUT_FULL = 36, BAR_OUT_EMPTY = 37, BAR_COUNT = 38 };
 
+// CG = 1: one CTA per SM, M = 128 MMAs. CG = 2: a cluster of two CTAs (one TPC) runs M = 256 MMAs
+// issued by the rank-0 CTA; each CTA encodes, stores and post-processes its own 128-row tile and
+// streams only ITS half of every weight chunk, so L2 -> SM weight traffic per row halves.
+// Barriers that gate the MMA issuer (feature/activation ready, accumulator drained, peer weights
+// landed) live in the rank-0 CTA and collect one arrival per warp from both CTAs; barriers the MMA
+// signals (accumulator full, weight stage free, feature buffer free) are multicast commits.
+template <int CG>
 __global__ void __launch_bounds__(kTcThreads, 1)
 nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // The model (incl. the chunk table) is a kernel parameter: the MMA and producer warps read it
@@ -144,15 +181,25 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // memory, or a single-lane issue loop, makes ptxas wrap every MMA in an R2UR/ELECT waterfall:
   // ~180 cycles per MMA instead of the 80-cycle tensor floor at N = 160; see profiles/.)
   extern __shared__ __align__(1024) unsigned char smem[];
+  constexpr int kStages = CG == 2 ? 8 : 4;
   const int H = m.H, NH = H / 2, numHidden = m.numHidden, numChunks = m.numChunks;
-  const TcSmem L = tcLayout(H, m.featKSteps, numHidden, numChunks);
+  const TcSmem L = tcLayout(H, m.featKSteps, numHidden, CG);
   const uint32_t sbase = smemAddr(smem);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  const uint32_t rank = (CG == 2) ? clusterCtaRank() : 0u;
   const uint32_t barBase = sbase + L.bars;
   auto bar = [&](int i) { return barBase + 8u * (uint32_t)i; };
+  // arrival on a barrier that gates the MMA issuer: lives in the rank-0 CTA
+  auto arriveIssuer = [&](int i) {
+    if (CG == 2) mbarArriveCluster(mapToCta(bar(i), 0u)); else mbarArrive(bar(i));
+  };
 
   const uint32_t count = io.count ? *io.count : io.countHost;
   const uint32_t numTiles = (count + kTcRows - 1) / kTcRows;
+  // work unit = CG consecutive tiles (one per CTA of the group); both CTAs of a pair run the same
+  // number of units, a tile index past the end is all padding rows
+  const uint32_t numUnits = (numTiles + CG - 1) / CG;
+  const uint32_t unit0 = blockIdx.x / CG, unitStride = gridDim.x / CG;
 
   // ---- one-time setup ----
   {
@@ -162,40 +209,63 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     for (int i = threadIdx.x; i < numHidden * H / 2; i += kTcThreads) sb[i] = gb[i];
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kTcStages; ++s) { mbarInit(bar(BAR_W_FULL + s), 1); mbarInit(bar(BAR_W_EMPTY + s), 1); }
+    for (int s = 0; s < kStages; ++s) { mbarInit(bar(BAR_W_FULL + s), 1); mbarInit(bar(BAR_W_EMPTY + s), 1); mbarInit(bar(BAR_PEER_W_FULL + s), 1); }
     for (int b = 0; b < 2; ++b) {
-      mbarInit(bar(BAR_FEAT_FULL + b), 32 * kEncodeWarps);
+      mbarInit(bar(BAR_FEAT_FULL + b), CG * kEncodeWarps);
       mbarInit(bar(BAR_FEAT_EMPTY + b), 1);
-      mbarInit(bar(BAR_ACT_READY + b), kEpiThreads);
+      mbarInit(bar(BAR_ACT_READY + b), CG * kEpiWarps);
     }
-    for (int b = 0; b < 3; ++b) { mbarInit(bar(BAR_ACC_FULL + b), 1); mbarInit(bar(BAR_ACC_EMPTY + b), kEpiThreads); }
+    for (int b = 0; b < 3; ++b) { mbarInit(bar(BAR_ACC_FULL + b), 1); mbarInit(bar(BAR_ACC_EMPTY + b), CG * kEpiWarps); }
     mbarInit(bar(BAR_OUT_FULL), 1);
-    mbarInit(bar(BAR_OUT_EMPTY), kEpiThreads / 2);
+    mbarInit(bar(BAR_OUT_EMPTY), CG * kEpiWarps / 2);
     fenceBarrierInit();
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + L.tmemSlot), "r"(kTmemCols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (CG == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + L.tmemSlot), "r"(kTmemCols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + L.tmemSlot), "r"(kTmemCols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tcFenceBefore();
   __syncthreads();
+  if (CG == 2) clusterSync();          // the peer's barriers are initialised before anyone signals them
   tcFenceAfter();
   const uint32_t tmemBase = *reinterpret_cast<volatile uint32_t*>(smem + L.tmemSlot);
-  const uint32_t stageBytes = kTcChunkKSteps * (uint32_t)NH * 32u;
+  const uint32_t stageBytes = kTcChunkKSteps * (uint32_t)(NH / CG) * 32u;
 
   if (warp == 0) {
     // ================= weight producer (converged warp, one elected lane issues) =================
     const bool leader = electOne();
     uint32_t stage = 0, phase = 0;
-    for (uint32_t tile = blockIdx.x; tile < numTiles; tile += gridDim.x) {
+    long long qEmpty = 0; const long long qStart = PROF_T(); (void)qStart;
+    for (uint32_t unit = unit0; unit < numUnits; unit += unitStride) {
       for (int c = 0; c < numChunks; ++c) {
-        const uint32_t bytes = (uint32_t)m.chunks[c].bytes16 * 16u;
-        mbarWait(bar(BAR_W_EMPTY + stage), phase ^ 1u);
+        const uint32_t bytes = (uint32_t)m.chunks[c].bytes16 * (16u / CG);      // this CTA's share of the chunk
+        { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_W_EMPTY + stage), phase ^ 1u); PROF_ADD(qEmpty, t0); }
         if (leader) {
           mbarArriveExpectTx(bar(BAR_W_FULL + stage), bytes);
-          bulkCopyG2S(sbase + L.ring + stage * stageBytes, m.wStream + m.chunks[c].offset, bytes, bar(BAR_W_FULL + stage));
+          bulkCopyG2S(sbase + L.ring + stage * stageBytes, m.wStream + m.chunks[c].offset + rank * bytes, bytes, bar(BAR_W_FULL + stage));
         }
-        if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+#ifdef B200PT_PROFILE
+    if (lane == 0) { unsigned long long* p = g_tcProf + blockIdx.x * 16 + 13; p[0] = qEmpty; p[1] = clock64() - qStart; }
+#endif
+    __syncwarp();
+  } else if (warp == 1 && rank != 0) {
+    // ================= weight-arrival relay (peer CTA of a pair) =================
+    // cp.async.bulk can only signal a barrier of its destination CTA, so this warp forwards
+    // "my half of the stage has landed" to the issuer's barrier in the rank-0 CTA.
+    uint32_t stage = 0, phase = 0;
+    for (uint32_t unit = unit0; unit < numUnits; unit += unitStride) {
+      for (int c = 0; c < numChunks; ++c) {
+        mbarWait<CG>(bar(BAR_W_FULL + stage), phase);
+        if (lane == 0) mbarArriveCluster(mapToCta(bar(BAR_PEER_W_FULL + stage), 0u));
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
     __syncwarp();
@@ -207,12 +277,12 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     uint32_t stage = 0, phase = 0;
     uint32_t actUse0 = 0, actUse1 = 0;     // completed waits on act_ready[part]
     uint32_t it = 0;
-    long long pFeat = 0, pAcc = 0, pAct = 0, pW = 0, pOutE = 0; const long long pStart = PROF_T();
-    for (uint32_t tile = blockIdx.x; tile < numTiles; tile += gridDim.x, ++it) {
+    long long pFeat = 0, pAcc = 0, pAct = 0, pW = 0, pOutE = 0, pPeer = 0, pIssue = 0; const long long pStart = PROF_T(); (void)pStart;
+    for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       const uint32_t fb = it & 1u;
       const uint32_t featLo = ((sbase + L.feat[fb]) >> 4);
-      const uint32_t jobBase = it * 2u * (uint32_t)numHidden;      // hidden jobs are numbered (tile, layer, half)
-      { const long long t0 = PROF_T(); mbarWait(bar(BAR_FEAT_FULL + fb), (it >> 1) & 1u); PROF_ADD(pFeat, t0); }
+      const uint32_t jobBase = it * 2u * (uint32_t)numHidden;      // hidden jobs are numbered (unit, layer, half)
+      { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_FEAT_FULL + fb), (it >> 1) & 1u); PROF_ADD(pFeat, t0); }
       for (int c = 0; c < numChunks; ++c) {
         const NifTcChunk& ch = m.chunks[c];
         const uint32_t ksteps = ch.ksteps, n8 = ch.n8, flags = ch.flags, waitAct = ch.waitAct;
@@ -222,38 +292,46 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         const uint32_t buf = job % 3u, accPhase = (job / 3u) & 1u;
         if (flags & kChFirst) {                                    // claim the accumulator
           const long long t0 = PROF_T();
-          if (isOut) { mbarWait(bar(BAR_OUT_EMPTY), (it & 1u) ^ 1u); PROF_ADD(pOutE, t0); }
-          else { mbarWait(bar(BAR_ACC_EMPTY + buf), accPhase ^ 1u); PROF_ADD(pAcc, t0); }
+          if (isOut) { mbarWait<CG>(bar(BAR_OUT_EMPTY), (it & 1u) ^ 1u); PROF_ADD(pOutE, t0); }
+          else { mbarWait<CG>(bar(BAR_ACC_EMPTY + buf), accPhase ^ 1u); PROF_ADD(pAcc, t0); }
         }
         { const long long t0 = PROF_T();
-          if (waitAct == 1) { mbarWait(bar(BAR_ACT_READY + 0), actUse0 & 1u); actUse0 += 1; }
-          else if (waitAct == 2) { mbarWait(bar(BAR_ACT_READY + 1), actUse1 & 1u); actUse1 += 1; }
+          if (waitAct == 1) { mbarWait<CG>(bar(BAR_ACT_READY + 0), actUse0 & 1u); actUse0 += 1; }
+          else if (waitAct == 2) { mbarWait<CG>(bar(BAR_ACT_READY + 1), actUse1 & 1u); actUse1 += 1; }
           PROF_ADD(pAct, t0); }
-        { const long long t0 = PROF_T(); mbarWait(bar(BAR_W_FULL + stage), phase); PROF_ADD(pW, t0); }
+        { const long long t0 = PROF_T();
+          mbarWait<CG>(bar(BAR_W_FULL + stage), phase);
+          PROF_ADD(pW, t0);
+          const long long t1 = PROF_T();
+          if (CG == 2) mbarWait<CG>(bar(BAR_PEER_W_FULL + stage), phase);
+          PROF_ADD(pPeer, t1); }
         tcFenceAfter();
         const uint32_t dT = tmemBase + (isOut ? kOutTmemCol : buf * (uint32_t)NH);
+        const uint32_t bRows = n8 * (8u / CG);                                        // rows of B this CTA holds
         uint32_t aLo = (((flags & kChSrcFeat) ? featLo : actLo) + ch.aOff16) | ((2048u >> 4) << 16);
-        uint32_t bLo = (ringLo + stage * (stageBytes >> 4)) | ((n8 * 8u) << 16);     // LBO = N * 16 bytes
-        const uint32_t idesc = umInstr(n8);
-        const uint32_t bStep = n8 * 16u;                                              // N * 32 bytes per K-step
+        uint32_t bLo = (ringLo + stage * (stageBytes >> 4)) | (bRows << 16);          // LBO = rows * 16 bytes
+        const uint32_t idesc = umInstr<CG>(n8);
+        const uint32_t bStep = bRows * 2u;                                            // rows * 32 bytes per K-step
         uint32_t acc = (flags & kChFirst) ? 0u : 1u;
+        const long long tIssue = PROF_T();
 #pragma unroll
         for (uint32_t j = 0; j < (uint32_t)kTcChunkKSteps; ++j) {
           if (j < ksteps) {
-            if (leader) tcMma(dT, aLo, bLo, kDescHi, idesc, acc);
+            if (leader) tcMma<CG>(dT, aLo, bLo, kDescHi, idesc, acc);
             aLo += 256u; bLo += bStep; acc = 1u;
           }
         }
         if (leader) {
-          tcCommit(bar(BAR_W_EMPTY + stage));
-          if (flags & kChLast) tcCommit(bar(isOut ? BAR_OUT_FULL : BAR_ACC_FULL + buf));
-          if (flags & kChLastFeatUse) tcCommit(bar(BAR_FEAT_EMPTY + fb));
+          tcCommit<CG>(bar(BAR_W_EMPTY + stage));
+          if (flags & kChLast) tcCommit<CG>(bar(isOut ? BAR_OUT_FULL : BAR_ACC_FULL + buf));
+          if (flags & kChLastFeatUse) tcCommit<CG>(bar(BAR_FEAT_EMPTY + fb));
         }
-        if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+        PROF_ADD(pIssue, tIssue);
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
 #ifdef B200PT_PROFILE
-    if (lane == 0) { unsigned long long* p = g_tcProf + blockIdx.x * 16; p[0] = clock64() - pStart; p[1] = pFeat; p[2] = pAcc; p[3] = pAct; p[4] = pW; p[5] = pOutE; p[6] = it; }
+    if (lane == 0) { unsigned long long* p = g_tcProf + blockIdx.x * 16; p[0] = clock64() - pStart; p[1] = pFeat; p[2] = pAcc; p[3] = pAct; p[4] = pW; p[5] = pOutE; p[6] = it; p[7] = pPeer; p[15] = pIssue; }
 #endif
     __syncwarp();
   } else if (warp < kFirstEpiWarp) {
@@ -261,17 +339,17 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     const uint32_t r = (warp - kFirstEncodeWarp) * 32u + lane;      // row inside the tile
     const int E = m.embeddingDim, featCores = m.featKSteps * 2;
     uint32_t it = 0;
-    for (uint32_t tile = blockIdx.x; tile < numTiles; tile += gridDim.x, ++it) {
+    for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       const uint32_t fb = it & 1u;
-      const uint32_t row = tile * kTcRows + r;
+      const uint32_t row = (unit * CG + rank) * kTcRows + r;
       float2 uv = make_float2(0.f, 0.f);
       if (row < count) uv = io.uv[row];
       __half f[kMaxFeatures];
 #pragma unroll
       for (int k = 0; k < kMaxFeatures; ++k) f[k] = __float2half_rn(0.f);
       nifEncode(uv.x, uv.y, E, [&](int k, __half v) { f[k] = v; });
-      // wait until the MMAs of the tile that last used this buffer are done with it
-      mbarWait(bar(BAR_FEAT_EMPTY + fb), ((it >> 1) & 1u) ^ 1u);
+      // wait until the MMAs of the unit that last used this buffer are done with it
+      mbarWait<CG>(bar(BAR_FEAT_EMPTY + fb), ((it >> 1) & 1u) ^ 1u);
       unsigned char* fbuf = smem + L.feat[fb];
       for (int kc = 0; kc < featCores; ++kc) {
         uint4 pk;
@@ -283,7 +361,8 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         *reinterpret_cast<uint4*>(fbuf + kc * 2048 + r * 16) = pk;
       }
       fenceProxyAsync();
-      mbarArrive(bar(BAR_FEAT_FULL + fb));
+      __syncwarp();
+      if (lane == 0) arriveIssuer(BAR_FEAT_FULL + fb);
     }
   } else {
     // ================= epilogue =================
@@ -296,13 +375,13 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     const uint32_t laneBase = tmemBase + ((quad * 32u) << 16);
     const __half2 zero2 = __float2half2_rn(0.f);
     uint32_t buf = 0, accPhase = 0, it = 0;
-    long long eWait = 0, eWork = 0, eOutWait = 0, eOutWork = 0; const long long eStart = PROF_T();
-    for (uint32_t tile = blockIdx.x; tile < numTiles; tile += gridDim.x, ++it) {
+    long long eWait = 0, eWork = 0, eOutWait = 0, eOutWork = 0; const long long eStart = PROF_T(); (void)eStart;
+    for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       for (int l = 0; l < numHidden; ++l) {
         const bool relu = m.relu[l] != 0;
         const unsigned char* biasRow = smem + L.bias + (uint32_t)l * (uint32_t)H * 2u;
         for (uint32_t h = 0; h < 2; ++h) {
-          { const long long t0 = PROF_T(); mbarWait(bar(BAR_ACC_FULL + buf), accPhase); PROF_ADD(eWait, t0); }
+          { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_ACC_FULL + buf), accPhase); PROF_ADD(eWait, t0); }
           const long long tw = PROF_T();
           tcFenceAfter();
           const uint32_t tBase = laneBase + buf * (uint32_t)NH + colHalf * colsMine;
@@ -332,25 +411,26 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
               *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
             }
           }
-          tcFenceBefore();
-          mbarArrive(bar(BAR_ACC_EMPTY + buf));
-          fenceProxyAsync();
-          mbarArrive(bar(BAR_ACT_READY + h));
+          tcFenceBefore();            // my TMEM reads are ordered before the arrive that frees the slot
+          fenceProxyAsync();          // my activation writes are visible to the tensor core (async proxy)
+          __syncwarp();
+          if (lane == 0) { arriveIssuer(BAR_ACC_EMPTY + buf); arriveIssuer(BAR_ACT_READY + h); }
           PROF_ADD(eWork, tw);
           if (++buf == 3u) { buf = 0; accPhase ^= 1u; }
         }
       }
       // output job: N = 16 accumulator, channels 0..3 are the network outputs (B,G,R[,unused])
       if (colHalf == 0) {
-        { const long long t0 = PROF_T(); mbarWait(bar(BAR_OUT_FULL), it & 1u); PROF_ADD(eOutWait, t0); }
+        { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_OUT_FULL), it & 1u); PROF_ADD(eOutWait, t0); }
         const long long tw = PROF_T();
         tcFenceAfter();
         uint32_t v[16];
         tcLoad16(laneBase + kOutTmemCol, v);
         tcWaitLoad();
         tcFenceBefore();
-        mbarArrive(bar(BAR_OUT_EMPTY));
-        const uint32_t row = tile * kTcRows + r;
+        __syncwarp();
+        if (lane == 0) arriveIssuer(BAR_OUT_EMPTY);
+        const uint32_t row = (unit * CG + rank) * kTcRows + r;
         if (row < count) {
           float out[3];
 #pragma unroll
@@ -375,18 +455,21 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // ---- teardown ----
   tcFenceBefore();
   __syncthreads();
+  if (CG == 2) clusterSync();        // the peer may still be signalling barriers here / reading its TMEM half
   tcFenceAfter();
   if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "r"(kTmemCols) : "memory");
+    if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "r"(kTmemCols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "r"(kTmemCols) : "memory");
   }
 }
 
-size_t nifTcSmemBytes(const NifTcModel& m) {
-  return (size_t)tcLayout(m.H, m.featKSteps, m.numHidden, m.numChunks).total + 1024;
+size_t nifTcSmemBytes(const NifTcModel& m, int cg) {
+  return (size_t)tcLayout(m.H, m.featKSteps, m.numHidden, cg).total + 1024;
 }
 
-cudaError_t prepareNifTc(size_t smemBytes) {
-  return cudaFuncSetAttribute(nif_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+cudaError_t prepareNifTc(size_t smemBytes, int cg) {
+  if (cg == 2) return cudaFuncSetAttribute(nif_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+  return cudaFuncSetAttribute(nif_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
 }
 
 #ifdef B200PT_PROFILE
@@ -395,13 +478,41 @@ extern "C" int b200pt_debug_tc_profile(unsigned long long* out, int n) {
 }
 #endif
 
-cudaError_t launchNifTc(const NifTcModel* modelDev, const NifTcModel& modelHost, const NifIo& io, int numSms, cudaStream_t stream) {
+// How many CTA pairs can be co-resident (cluster launch of 2 CTAs, 1 CTA per SM).
+int nifTcMaxPairs(const NifTcModel& m) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2, 1, 1);
+  cfg.blockDim = dim3(kTcThreads, 1, 1);
+  cfg.dynamicSmemBytes = nifTcSmemBytes(m, 2);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, nif_tc_kernel<2>, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int cg, int numSms, int maxPairs, cudaStream_t stream) {
   if (io.countHost == 0) return cudaSuccess;
-  const size_t smem = nifTcSmemBytes(modelHost);
-  uint32_t tilesMax = (io.countHost + kTcRows - 1) / kTcRows;
-  uint32_t grid = tilesMax < (uint32_t)numSms ? tilesMax : (uint32_t)numSms;
-  (void)modelDev;
-  nif_tc_kernel<<<grid, kTcThreads, smem, stream>>>(modelHost, io);
+  const size_t smem = nifTcSmemBytes(model, cg);
+  const uint32_t tilesMax = (io.countHost + kTcRows - 1) / kTcRows;
+  if (cg == 2) {
+    const uint32_t pairsMax = (tilesMax + 1) / 2;
+    const uint32_t pairs = pairsMax < (uint32_t)maxPairs ? pairsMax : (uint32_t)maxPairs;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs, 1, 1);
+    cfg.blockDim = dim3(kTcThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, nif_tc_kernel<2>, model, io);
+  }
+  const uint32_t grid = tilesMax < (uint32_t)numSms ? tilesMax : (uint32_t)numSms;
+  nif_tc_kernel<1><<<grid, kTcThreads, smem, stream>>>(model, io);
   return cudaGetLastError();
 }
 
