@@ -71,6 +71,7 @@ bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200
                            (srcFeat ? kChSrcFeat : 0) | (isOut ? kChOut : 0));
       ch.waitAct = (ks0 == 0) ? (uint8_t)waitAct : 0;
       ch.layer = (uint8_t)layer; ch.half = (uint8_t)half;
+      ch.slot = (uint8_t)((2 * layer + half) % 3); ch.slotUse = (uint8_t)((2 * layer + half) / 3);
       stream.resize(stream.size() + bytes, 0);
       uint16_t* dst = reinterpret_cast<uint16_t*>(stream.data() + ch.offset);
       const HostLayer& L = ls[layer];
@@ -123,6 +124,7 @@ bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200
   if (overflow) return false;
   tm.chunks[lastFeatChunk].flags |= kChLastFeatUse;
   tm.numChunks = nChunks;
+  for (int j = 0; j < 2 * numHidden; ++j) tm.slotUses[j % 3] += 1;
   const HostLayer& last = ls.back();
   tm.outC = last.out; tm.finalRelu = last.relu; tm.finalHasBias = last.hasBias;
   for (int j = 0; j < 4; ++j) tm.bOut[j] = j < last.out ? hostHalfToFloat(last.b[j]) : 0.f;

@@ -62,13 +62,16 @@ struct NifTcChunk {        // 16 bytes, read as one uint4 by the MMA thread
                            // last reader of the feature buffer in the tile, output-layer job
   uint8_t waitAct;         // 0 none, 1 wait for activation columns [0,H/2), 2 for [H/2,H): set on the
                            // first chunk of a layer that reads the range
-  uint8_t layer, half, pad0, pad1;
+  uint8_t layer, half;
+  uint8_t slot;            // TMEM accumulator slot of the chunk's job: (2 * layer + half) % 3
+  uint8_t slotUse;         // how many earlier jobs of the tile used that slot: (2 * layer + half) / 3
 };
 static_assert(sizeof(NifTcChunk) == 16, "chunk table entries are loaded as uint4");
 struct NifTcModel {
   int numHidden, H, nFeat, embeddingDim, featKSteps, numChunks;
   int relu[kMaxNifLayers];
   int outC, finalRelu;
+  int slotUses[3];             // jobs per tile on each accumulator slot
   const uint8_t* wStream;      // packed chunks (device)
   const __half* bias;          // [numHidden][H] (device; zeros where a layer has no bias)
   float bOut[4];

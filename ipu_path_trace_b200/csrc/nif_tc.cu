@@ -281,15 +281,14 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       const uint32_t fb = it & 1u;
       const uint32_t featLo = ((sbase + L.feat[fb]) >> 4);
-      const uint32_t jobBase = it * 2u * (uint32_t)numHidden;      // hidden jobs are numbered (unit, layer, half)
       { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_FEAT_FULL + fb), (it >> 1) & 1u); PROF_ADD(pFeat, t0); }
       for (int c = 0; c < numChunks; ++c) {
         const NifTcChunk& ch = m.chunks[c];
         const uint32_t ksteps = ch.ksteps, n8 = ch.n8, flags = ch.flags, waitAct = ch.waitAct;
         const bool isOut = (flags & kChOut) != 0;
-        // the two half-jobs of a layer accumulate concurrently (K order above): slot from the job number
-        const uint32_t job = jobBase + 2u * ch.layer + ch.half;
-        const uint32_t buf = job % 3u, accPhase = (job / 3u) & 1u;
+        // the two half-jobs of a layer accumulate concurrently (K order above): the accumulator slot
+        // and how often the slot was used before in this tile come precomputed with the chunk
+        const uint32_t buf = ch.slot, accPhase = (it * m.slotUses[ch.slot] + ch.slotUse) & 1u;
         if (flags & kChFirst) {                                    // claim the accumulator
           const long long t0 = PROF_T();
           if (isOut) { mbarWait<CG>(bar(BAR_OUT_EMPTY), (it & 1u) ^ 1u); PROF_ADD(pOutE, t0); }
@@ -374,13 +373,15 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     const uint32_t groups = colsMine / 16u;               // <= 5
     const uint32_t laneBase = tmemBase + ((quad * 32u) << 16);
     const __half2 zero2 = __float2half2_rn(0.f);
-    uint32_t buf = 0, accPhase = 0, it = 0;
+    uint32_t it = 0;
     long long eWait = 0, eWork = 0, eOutWait = 0, eOutWork = 0; const long long eStart = PROF_T(); (void)eStart;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       for (int l = 0; l < numHidden; ++l) {
         const bool relu = m.relu[l] != 0;
         const unsigned char* biasRow = smem + L.bias + (uint32_t)l * (uint32_t)H * 2u;
         for (uint32_t h = 0; h < 2; ++h) {
+          const uint32_t jobInTile = 2u * (uint32_t)l + h;
+          const uint32_t buf = jobInTile % 3u, accPhase = (it * m.slotUses[buf] + jobInTile / 3u) & 1u;
           { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_ACC_FULL + buf), accPhase); PROF_ADD(eWait, t0); }
           const long long tw = PROF_T();
           tcFenceAfter();
@@ -416,7 +417,6 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           __syncwarp();
           if (lane == 0) { arriveIssuer(BAR_ACC_EMPTY + buf); arriveIssuer(BAR_ACT_READY + h); }
           PROF_ADD(eWork, tw);
-          if (++buf == 3u) { buf = 0; accPhase ^= 1u; }
         }
       }
       // output job: N = 16 accumulator, channels 0..3 are the network outputs (B,G,R[,unused])
