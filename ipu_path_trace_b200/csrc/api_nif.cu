@@ -39,9 +39,11 @@ std::string tcEligibility(const std::vector<HostLayer>& ls, int nFeat) {
 // Builds the tcgen05 kernel's model: the chunk table and the packed weight stream. Every (layer,
 // N-range, K-range) chunk is the exact shared-memory image of a K-major UMMA B operand, in MMA issue
 // order; for a CTA pair (cg == 2) a chunk is stored as [image of CTA 0's N/2 rows | image of CTA 1's].
-bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200pt_nif_desc& nif, int cg, NifTcModel& tm,
+bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200pt_nif_desc& nif, int cg, int ts, int kc, NifTcModel& tm,
                   std::vector<uint8_t>& stream) {
   std::memset(&tm, 0, sizeof(tm));
+  tm.cg = cg; tm.ts = ts; tm.kc = kc;
+  const int numSlots = ts ? 2 : 3;
   const int numHidden = (int)ls.size() - 1;
   const int H = ls[0].out, NH = H / 2;
   const int featKSteps = (nFeat + 15) / 16;
@@ -57,9 +59,9 @@ bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200
   // Keras kernel (-1 = zero pad).
   auto addBlock = [&](int layer, int half, int col0, int nCols, bool srcFeat, int kstepBegin, int kstepCount, auto rowOfK,
                       bool firstOfJob, bool lastOfJob, int waitAct, bool isOut) {
-    for (int ks0 = 0; ks0 < kstepCount; ks0 += kTcChunkKSteps) {
+    for (int ks0 = 0; ks0 < kstepCount; ks0 += kc) {
       if (nChunks == kTcMaxChunks) { overflow = true; return; }
-      const int ks = std::min(kTcChunkKSteps, kstepCount - ks0);
+      const int ks = std::min(kc, kstepCount - ks0);
       NifTcChunk& ch = tm.chunks[nChunks++];
       std::memset(&ch, 0, sizeof(ch));
       ch.offset = (uint32_t)stream.size();
@@ -71,7 +73,7 @@ bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200
                            (srcFeat ? kChSrcFeat : 0) | (isOut ? kChOut : 0));
       ch.waitAct = (ks0 == 0) ? (uint8_t)waitAct : 0;
       ch.layer = (uint8_t)layer; ch.half = (uint8_t)half;
-      ch.slot = (uint8_t)((2 * layer + half) % 3); ch.slotUse = (uint8_t)((2 * layer + half) / 3);
+      ch.slot = (uint8_t)((2 * layer + half) % numSlots); ch.slotUse = (uint8_t)((2 * layer + half) / numSlots);
       stream.resize(stream.size() + bytes, 0);
       uint16_t* dst = reinterpret_cast<uint16_t*>(stream.data() + ch.offset);
       const HostLayer& L = ls[layer];
@@ -124,7 +126,7 @@ bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200
   if (overflow) return false;
   tm.chunks[lastFeatChunk].flags |= kChLastFeatUse;
   tm.numChunks = nChunks;
-  for (int j = 0; j < 2 * numHidden; ++j) tm.slotUses[j % 3] += 1;
+  for (int j = 0; j < 2 * numHidden; ++j) tm.slotUses[j % numSlots] += 1;
   const HostLayer& last = ls.back();
   tm.outC = last.out; tm.finalRelu = last.relu; tm.finalHasBias = last.hasBias;
   for (int j = 0; j < 4; ++j) tm.bOut[j] = j < last.out ? hostHalfToFloat(last.b[j]) : 0.f;
@@ -209,24 +211,30 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
     for (int l = 0; l < numHidden; ++l) for (int i = 0; i < H; ++i) bias[(size_t)l * H + i] = ls[l].b[i];
     CU(c, c->tcBias.alloc(bias.size()));
     CU(c, cudaMemcpy(c->tcBias.p, bias.data(), bias.size() * 2, cudaMemcpyHostToDevice));
-    for (int cg = 1; cg <= 2 && c->tcOk; ++cg) {
-      NifTcModel& tm = c->tcHost[cg - 1];
-      std::vector<uint8_t> stream;
-      if (!buildTcModel(ls, nFeat, E, *nif, cg, tm, stream)) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; break; }
-      DevBuf<uint8_t>& dev = c->tcStream[cg - 1];
-      CU(c, dev.alloc(stream.size()));
-      CU(c, cudaMemcpy(dev.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
-      tm.wStream = dev.p; tm.bias = c->tcBias.p;
-      const size_t smem = nifTcSmemBytes(tm, cg);
-      if (smem > 227 * 1024) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; break; }
-      CU(c, prepareNifTc(smem, cg));
+    // Kernel variant. Default: activations in tensor memory, 10 K-steps per chunk. B200PT_NIF_MODE =
+    // ss1 | ss2 | ts5 | ts10 selects another one (A/B measurements and the parity tests of each variant).
+    int cg = 1, ts = 1, kc = 10;
+    if (const char* e = getenv("B200PT_NIF_MODE")) {
+      const std::string mode(e);
+      if (mode == "ss1") { cg = 1; ts = 0; kc = 5; }
+      else if (mode == "ss2") { cg = 2; ts = 0; kc = 5; }
+      else if (mode == "ts5") { cg = 1; ts = 1; kc = 5; }
+      else if (mode == "ts10") { cg = 1; ts = 1; kc = 10; }
+      else return c->fail(B200PT_ERR_INVALID, "B200PT_NIF_MODE must be ss1, ss2, ts5 or ts10");
     }
-    if (c->tcOk) {
-      // CTA pairs (cta_group::2) halve the L2 -> SM weight traffic per row; use them when every SM can
-      // be part of a resident pair. B200PT_NIF_CG=1|2 overrides (A/B measurements).
-      c->tcMaxPairs = nifTcMaxPairs(c->tcHost[1]);
-      c->tcCg = 1;   // measured (profiles/): pairs are not yet faster than single CTAs; B200PT_NIF_CG=2 selects them
-      if (const char* e = getenv("B200PT_NIF_CG")) { if (e[0] == '1') c->tcCg = 1; else if (e[0] == '2' && c->tcMaxPairs > 0) c->tcCg = 2; }
+    NifTcModel& tm = c->tcHost;
+    std::vector<uint8_t> stream;
+    if (!buildTcModel(ls, nFeat, E, *nif, cg, ts, kc, tm, stream)) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; }
+    else {
+      CU(c, c->tcStream.alloc(stream.size()));
+      CU(c, cudaMemcpy(c->tcStream.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
+      tm.wStream = c->tcStream.p; tm.bias = c->tcBias.p;
+      if (nifTcSmemBytes(tm) > 227 * 1024 || nifTcStages(tm) < 2) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; }
+      else {
+        CU(c, prepareNifTc(tm));
+        c->tcMaxPairs = cg == 2 ? nifTcMaxPairs(tm) : 0;
+        if (cg == 2 && c->tcMaxPairs < 1) { c->tcOk = false; c->tcWhyNot = "no co-resident CTA pairs on this device"; }
+      }
     }
   }
   if (c->cfg.nif_impl == B200PT_NIF_TCGEN05 && !c->tcOk)
@@ -247,7 +255,7 @@ int launchNif(b200pt_ctx* c, const NifIo& io, int impl, int* used) {
   if (impl == B200PT_NIF_AUTO) impl = c->tcOk ? B200PT_NIF_TCGEN05 : B200PT_NIF_SIMT;
   if (impl == B200PT_NIF_TCGEN05) {
     if (!c->tcOk) return c->fail(B200PT_ERR_INVALID, "tcgen05 NIF path unavailable for this model: %s", c->tcWhyNot.c_str());
-    CU(c, launchNifTc(c->tcHost[c->tcCg - 1], io, c->tcCg, c->numSms, c->tcMaxPairs, c->stream));
+    CU(c, launchNifTc(c->tcHost, io, c->numSms, c->tcMaxPairs, c->stream));
   } else if (impl == B200PT_NIF_SIMT) {
     CU(c, launchNifSimt(c->simt, io, c->stream));
   } else {

@@ -80,9 +80,9 @@ struct b200pt_ctx {
   DevBuf<float> simtParams;
   bool tcOk = false;
   std::string tcWhyNot;
-  NifTcModel tcHost[2]{};                // [0] single-CTA MMAs, [1] CTA pairs (cta_group::2)
-  DevBuf<uint8_t> tcStream[2];
-  int tcCg = 1, tcMaxPairs = 0;
+  NifTcModel tcHost{};
+  DevBuf<uint8_t> tcStream;
+  int tcMaxPairs = 0;
   DevBuf<__half> tcBias;
 
   b200pt_counters counters{};

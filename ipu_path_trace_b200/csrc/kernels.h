@@ -49,7 +49,6 @@ size_t nifSimtSmemBytes(const NifSimtModel& m);
 // Description used by the tcgen05 kernel: every Dense layer on the tensor cores. A hidden layer's
 // N = H outputs are computed as two half "jobs" (N = H/2 each, own TMEM accumulator); the final
 // layer (<= 4 outputs) is one job padded to N = 16.
-constexpr int kTcChunkKSteps = 5;     // K-steps (of 16) per weight-ring stage
 constexpr int kTcMaxChunks = 160;
 enum : uint8_t { kChFirst = 1, kChLast = 2, kChSrcFeat = 4, kChLastFeatUse = 8, kChOut = 16 };
 struct NifTcChunk {        // 16 bytes, read as one uint4 by the MMA thread
@@ -72,6 +71,7 @@ struct NifTcModel {
   int relu[kMaxNifLayers];
   int outC, finalRelu;
   int slotUses[3];             // jobs per tile on each accumulator slot
+  int cg, ts, kc;              // kernel variant: CTAs per MMA group, activations in TMEM, K-steps per chunk
   const uint8_t* wStream;      // packed chunks (device)
   const __half* bias;          // [numHidden][H] (device; zeros where a layer has no bias)
   float bOut[4];
@@ -80,10 +80,10 @@ struct NifTcModel {
   int logToneMap;
   NifTcChunk chunks[kTcMaxChunks];
 };
-// cg = CTAs per MMA group: 1, or 2 = CTA pairs (cluster of 2, tcgen05 cta_group::2)
-cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int cg, int numSms, int maxPairs, cudaStream_t stream);
-size_t nifTcSmemBytes(const NifTcModel& m, int cg);
-cudaError_t prepareNifTc(size_t smemBytes, int cg);
+cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int numSms, int maxPairs, cudaStream_t stream);
+size_t nifTcSmemBytes(const NifTcModel& m);
+int nifTcStages(const NifTcModel& m);
+cudaError_t prepareNifTc(const NifTcModel& m);
 int nifTcMaxPairs(const NifTcModel& m);
 
 // n rows of 4E binary16 features (as fp32) for the KAT entry point.

@@ -33,7 +33,6 @@ constexpr int kTcThreads = 32 * (2 + kEncodeWarps + kEpiWarps);
 constexpr int kFirstEncodeWarp = 2;
 constexpr int kFirstEpiWarp = 2 + kEncodeWarps;
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kOutTmemCol = 480;      // the N=16 output accumulator sits after the three H/2 <= 160 column slots
 // weight-ring depth: the CTA pair holds half a chunk per CTA, so the same bytes give twice the stages
 
 
@@ -109,6 +108,28 @@ __device__ __forceinline__ void tcMma(uint32_t dTmem, uint32_t aLo, uint32_t bLo
         "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
         ::"r"(dTmem), "r"(aLo), "r"(bLo), "r"(descHi), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Same with the A operand in tensor memory (128 lanes x 8 columns of packed binary16 pairs per K-step).
+template <int CG>
+__device__ __forceinline__ void tcMmaTs(uint32_t dTmem, uint32_t aTmem, uint32_t bLo, uint32_t descHi, uint32_t idesc, uint32_t accumulate) {
+  if (CG == 2)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(dTmem), "r"(aTmem), "r"(bLo), "r"(descHi), "r"(idesc), "r"(accumulate) : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(dTmem), "r"(aTmem), "r"(bLo), "r"(descHi), "r"(idesc), "r"(accumulate) : "memory");
+}
+// registers -> tensor memory: 8 consecutive 32-bit columns of this thread's lane
+__device__ __forceinline__ void tcStore8(uint32_t taddr, const uint32_t (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+__device__ __forceinline__ void tcWaitStore() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tcLoad16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
@@ -145,19 +166,29 @@ __device__ unsigned long long g_tcProf[148 * 16];
 struct TcSmem {
   // byte offsets from the dynamic shared memory base
   uint32_t act, feat[2], ring, bias, bars, tmemSlot, total;
+  uint32_t stages, stageBytes;
 };
 // cg = CTAs per MMA group (1, or 2 for a CTA pair): the ring holds 1/cg of every chunk per CTA.
-__host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden, int cg) {
+// ts = activations live in tensor memory (A operand from TMEM), so no activation buffer in smem and
+// the weight ring takes everything that is left. kc = K-steps per chunk = per ring stage.
+__host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden, int cg, int ts, int kc) {
   TcSmem s;
   uint32_t o = 0;
-  s.act = o; o += (uint32_t)H * kTcRows * 2;
+  s.act = o; if (!ts) o += (uint32_t)H * kTcRows * 2;
   s.feat[0] = o; o += (uint32_t)featKSteps * 4096;
   s.feat[1] = o; o += (uint32_t)featKSteps * 4096;
-  s.ring = o; o += (uint32_t)(cg == 2 ? 8 : 4) * kTcChunkKSteps * (uint32_t)(H / 2 / cg) * 32;
   s.bias = o; o += (uint32_t)numHidden * H * 2;
   o = (o + 15u) & ~15u;
   s.bars = o; o += 48 * 8;
   s.tmemSlot = o; o += 16;
+  o = (o + 127u) & ~127u;
+  s.ring = o;
+  s.stageBytes = (uint32_t)kc * (uint32_t)(H / 2 / cg) * 32u;
+  const uint32_t budget = 232448u - 1024u;                       // 227 KB per CTA minus the alignment slack
+  uint32_t st = (budget - o) / s.stageBytes;
+  if (!ts) st = cg == 2 ? 8u : 4u;
+  s.stages = st > 8u ? 8u : st;
+  o += s.stages * s.stageBytes;
   s.total = o;
   return s;
 }
@@ -172,7 +203,12 @@ enum { BAR_W_FULL = 0, BAR_W_EMPTY = 8, BAR_PEER_W_FULL = 16, BAR_FEAT_FULL = 24
 // Barriers that gate the MMA issuer (feature/activation ready, accumulator drained, peer weights
 // landed) live in the rank-0 CTA and collect one arrival per warp from both CTAs; barriers the MMA
 // signals (accumulator full, weight stage free, feature buffer free) are multicast commits.
-template <int CG>
+// TS: hidden activations are kept in tensor memory as packed binary16 (the A operand of the next
+// layer comes from TMEM, the epilogue writes it with tcgen05.st): no activation traffic in shared
+// memory, and the 80 KB it occupied go to the weight ring. TMEM then holds activations (H/2 columns),
+// two accumulator slots (one per half-job) and the output accumulator.
+// KC: K-steps per weight chunk (= MMAs per ring stage).
+template <int CG, bool TS, int KC>
 __global__ void __launch_bounds__(kTcThreads, 1)
 nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // The model (incl. the chunk table) is a kernel parameter: the MMA and producer warps read it
@@ -181,9 +217,12 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // memory, or a single-lane issue loop, makes ptxas wrap every MMA in an R2UR/ELECT waterfall:
   // ~180 cycles per MMA instead of the 80-cycle tensor floor at N = 160; see profiles/.)
   extern __shared__ __align__(1024) unsigned char smem[];
-  constexpr int kStages = CG == 2 ? 8 : 4;
+  constexpr uint32_t kSlots = TS ? 2u : 3u;             // TMEM accumulator slots of H/2 columns
   const int H = m.H, NH = H / 2, numHidden = m.numHidden, numChunks = m.numChunks;
-  const TcSmem L = tcLayout(H, m.featKSteps, numHidden, CG);
+  const TcSmem L = tcLayout(H, m.featKSteps, numHidden, CG, TS ? 1 : 0, KC);
+  const int kStages = (int)L.stages;
+  const uint32_t accCol0 = TS ? (uint32_t)NH : 0u;      // TS: columns [0, H/2) hold the activations
+  const uint32_t outCol = 3u * (uint32_t)NH;            // output accumulator (16 columns)
   const uint32_t sbase = smemAddr(smem);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   const uint32_t rank = (CG == 2) ? clusterCtaRank() : 0u;
@@ -215,7 +254,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       mbarInit(bar(BAR_FEAT_EMPTY + b), 1);
       mbarInit(bar(BAR_ACT_READY + b), CG * kEpiWarps);
     }
-    for (int b = 0; b < 3; ++b) { mbarInit(bar(BAR_ACC_FULL + b), 1); mbarInit(bar(BAR_ACC_EMPTY + b), CG * kEpiWarps); }
+    for (int b = 0; b < (int)kSlots; ++b) { mbarInit(bar(BAR_ACC_FULL + b), 1); mbarInit(bar(BAR_ACC_EMPTY + b), CG * kEpiWarps); }
     mbarInit(bar(BAR_OUT_FULL), 1);
     mbarInit(bar(BAR_OUT_EMPTY), CG * kEpiWarps / 2);
     fenceBarrierInit();
@@ -234,7 +273,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   if (CG == 2) clusterSync();          // the peer's barriers are initialised before anyone signals them
   tcFenceAfter();
   const uint32_t tmemBase = *reinterpret_cast<volatile uint32_t*>(smem + L.tmemSlot);
-  const uint32_t stageBytes = kTcChunkKSteps * (uint32_t)(NH / CG) * 32u;
+  const uint32_t stageBytes = L.stageBytes;
 
   if (warp == 0) {
     // ================= weight producer (converged warp, one elected lane issues) =================
@@ -305,19 +344,32 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           if (CG == 2) mbarWait<CG>(bar(BAR_PEER_W_FULL + stage), phase);
           PROF_ADD(pPeer, t1); }
         tcFenceAfter();
-        const uint32_t dT = tmemBase + (isOut ? kOutTmemCol : buf * (uint32_t)NH);
+        const uint32_t dT = tmemBase + (isOut ? outCol : accCol0 + buf * (uint32_t)NH);
         const uint32_t bRows = n8 * (8u / CG);                                        // rows of B this CTA holds
         uint32_t aLo = (((flags & kChSrcFeat) ? featLo : actLo) + ch.aOff16) | ((2048u >> 4) << 16);
+        uint32_t aTm = tmemBase + (uint32_t)(ch.aOff16 >> 8) * 8u;                     // TS: K-step k -> columns [8k, 8k+8)
+        const bool aFromTmem = TS && !(flags & kChSrcFeat);
         uint32_t bLo = (ringLo + stage * (stageBytes >> 4)) | (bRows << 16);          // LBO = rows * 16 bytes
         const uint32_t idesc = umInstr<CG>(n8);
         const uint32_t bStep = bRows * 2u;                                            // rows * 32 bytes per K-step
         uint32_t acc = (flags & kChFirst) ? 0u : 1u;
         const long long tIssue = PROF_T();
+        // Two separate loops: a predicated-off twin UTCHMMA still occupies a tensor-queue slot.
+        if (aFromTmem) {
 #pragma unroll
-        for (uint32_t j = 0; j < (uint32_t)kTcChunkKSteps; ++j) {
-          if (j < ksteps) {
-            if (leader) tcMma<CG>(dT, aLo, bLo, kDescHi, idesc, acc);
-            aLo += 256u; bLo += bStep; acc = 1u;
+          for (uint32_t j = 0; j < (uint32_t)KC; ++j) {
+            if (j < ksteps) {
+              if (leader) tcMmaTs<CG>(dT, aTm, bLo, kDescHi, idesc, acc);
+              aTm += 8u; bLo += bStep; acc = 1u;
+            }
+          }
+        } else {
+#pragma unroll
+          for (uint32_t j = 0; j < (uint32_t)KC; ++j) {
+            if (j < ksteps) {
+              if (leader) tcMma<CG>(dT, aLo, bLo, kDescHi, idesc, acc);
+              aLo += 256u; bLo += bStep; acc = 1u;
+            }
           }
         }
         if (leader) {
@@ -381,11 +433,11 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         const unsigned char* biasRow = smem + L.bias + (uint32_t)l * (uint32_t)H * 2u;
         for (uint32_t h = 0; h < 2; ++h) {
           const uint32_t jobInTile = 2u * (uint32_t)l + h;
-          const uint32_t buf = jobInTile % 3u, accPhase = (it * m.slotUses[buf] + jobInTile / 3u) & 1u;
+          const uint32_t buf = jobInTile % kSlots, accPhase = (it * m.slotUses[buf] + jobInTile / kSlots) & 1u;
           { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_ACC_FULL + buf), accPhase); PROF_ADD(eWait, t0); }
           const long long tw = PROF_T();
           tcFenceAfter();
-          const uint32_t tBase = laneBase + buf * (uint32_t)NH + colHalf * colsMine;
+          const uint32_t tBase = laneBase + accCol0 + buf * (uint32_t)NH + colHalf * colsMine;
           const uint32_t colBase = h * (uint32_t)NH + colHalf * colsMine;      // output-neuron index of my first column
           // software pipeline: the load of group g+1 is in flight while group g is converted and stored
           uint32_t v[2][16];
@@ -407,13 +459,18 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
                 if (relu) hv = __hmax2(hv, zero2);
                 packed[q] = *reinterpret_cast<uint32_t*>(&hv);
               }
-              unsigned char* dst = smem + L.act + (c0 / 8u) * 2048u + r * 16u;
-              *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-              *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+              if (TS) {
+                tcStore8(laneBase + c0 / 2u, packed);            // neuron c -> TMEM column c / 2 (binary16 pairs)
+              } else {
+                unsigned char* dst = smem + L.act + (c0 / 8u) * 2048u + r * 16u;
+                *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+              }
             }
           }
-          tcFenceBefore();            // my TMEM reads are ordered before the arrive that frees the slot
-          fenceProxyAsync();          // my activation writes are visible to the tensor core (async proxy)
+          if (TS) tcWaitStore();      // my activation columns are in tensor memory
+          else fenceProxyAsync();     // my activation writes are visible to the tensor core (async proxy)
+          tcFenceBefore();            // my TMEM accesses are ordered before the arrives below
           __syncwarp();
           if (lane == 0) { arriveIssuer(BAR_ACC_EMPTY + buf); arriveIssuer(BAR_ACT_READY + h); }
           PROF_ADD(eWork, tw);
@@ -425,7 +482,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         const long long tw = PROF_T();
         tcFenceAfter();
         uint32_t v[16];
-        tcLoad16(laneBase + kOutTmemCol, v);
+        tcLoad16(laneBase + outCol, v);
         tcWaitLoad();
         tcFenceBefore();
         __syncwarp();
@@ -463,13 +520,21 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   }
 }
 
-size_t nifTcSmemBytes(const NifTcModel& m, int cg) {
-  return (size_t)tcLayout(m.H, m.featKSteps, m.numHidden, cg).total + 1024;
+size_t nifTcSmemBytes(const NifTcModel& m) {
+  return (size_t)tcLayout(m.H, m.featKSteps, m.numHidden, m.cg, m.ts, m.kc).total + 1024;
 }
+int nifTcStages(const NifTcModel& m) { return (int)tcLayout(m.H, m.featKSteps, m.numHidden, m.cg, m.ts, m.kc).stages; }
 
-cudaError_t prepareNifTc(size_t smemBytes, int cg) {
-  if (cg == 2) return cudaFuncSetAttribute(nif_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-  return cudaFuncSetAttribute(nif_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+namespace {
+using KernelFn = void (*)(const NifTcModel, const NifIo);
+KernelFn pickKernel(const NifTcModel& m) {
+  if (m.ts) return m.kc == 10 ? nif_tc_kernel<1, true, 10> : nif_tc_kernel<1, true, 5>;
+  return m.cg == 2 ? nif_tc_kernel<2, false, 5> : nif_tc_kernel<1, false, 5>;
+}
+} // namespace
+
+cudaError_t prepareNifTc(const NifTcModel& m) {
+  return cudaFuncSetAttribute(pickKernel(m), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nifTcSmemBytes(m));
 }
 
 #ifdef B200PT_PROFILE
@@ -483,37 +548,36 @@ int nifTcMaxPairs(const NifTcModel& m) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2, 1, 1);
   cfg.blockDim = dim3(kTcThreads, 1, 1);
-  cfg.dynamicSmemBytes = nifTcSmemBytes(m, 2);
+  cfg.dynamicSmemBytes = nifTcSmemBytes(m);
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, nif_tc_kernel<2>, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+  if (cudaOccupancyMaxActiveClusters(&n, pickKernel(m), &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
   return n;
 }
 
-cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int cg, int numSms, int maxPairs, cudaStream_t stream) {
+cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int numSms, int maxPairs, cudaStream_t stream) {
   if (io.countHost == 0) return cudaSuccess;
-  const size_t smem = nifTcSmemBytes(model, cg);
+  const size_t smem = nifTcSmemBytes(model);
   const uint32_t tilesMax = (io.countHost + kTcRows - 1) / kTcRows;
-  if (cg == 2) {
+  uint32_t grid = tilesMax < (uint32_t)numSms ? tilesMax : (uint32_t)numSms;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kTcThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  cfg.attrs = attr; cfg.numAttrs = 0;
+  if (model.cg == 2) {
     const uint32_t pairsMax = (tilesMax + 1) / 2;
-    const uint32_t pairs = pairsMax < (uint32_t)maxPairs ? pairsMax : (uint32_t)maxPairs;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * pairs, 1, 1);
-    cfg.blockDim = dim3(kTcThreads, 1, 1);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    grid = 2 * (pairsMax < (uint32_t)maxPairs ? pairsMax : (uint32_t)maxPairs);
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, nif_tc_kernel<2>, model, io);
+    cfg.numAttrs = 1;
   }
-  const uint32_t grid = tilesMax < (uint32_t)numSms ? tilesMax : (uint32_t)numSms;
-  nif_tc_kernel<1><<<grid, kTcThreads, smem, stream>>>(model, io);
-  return cudaGetLastError();
+  cfg.gridDim = dim3(grid, 1, 1);
+  return cudaLaunchKernelEx(&cfg, pickKernel(model), model, io);
 }
 
 } // namespace b2

@@ -52,15 +52,15 @@ __global__ void __launch_bounds__(256, 1) bench(int mode, int N, int ksteps, int
     uint32_t leader; asm volatile("{ .reg .pred p; elect.sync _|p, 0xffffffff; selp.u32 %0, 1, 0, p; }" : "=r"(leader));
     const long long t0 = clock64();
     for (int r = 0; r < reps; ++r) {
-      const uint32_t d = tmem + (r & 1) * 160;
+      const uint32_t d = tmem + 160 + (r & 1) * 160;
       if (mode == 0) {
         for (int j = 0; j < ksteps; ++j) { if (leader) mmaSS(d, desc(aBase + j * 4096, 2048, 128, 0), desc(bBase + (j & 7) * N * 32, N * 16, 128, 0), idesc, j > 0); }
       } else if (mode == 1) {
         for (int j = 0; j < ksteps; ++j) { if (leader) mmaSS(d, desc(aBase + (j >> 2) * 16384 + (j & 3) * 32, 16, 1024, 2), desc(bBase + ((j >> 2) & 1) * N * 128 + (j & 3) * 32, 16, 1024, 2), idesc, j > 0); }
       } else if (mode == 2) {
-        for (int j = 0; j < ksteps; ++j) { if (leader) mmaTS(d, tmem + 320 + j * 8, desc(bBase + (j & 7) * N * 32, N * 16, 128, 0), idesc, j > 0); }
+        for (int j = 0; j < ksteps; ++j) { if (leader) mmaTS(d, tmem + j * 8, desc(bBase + (j & 7) * N * 32, N * 16, 128, 0), idesc, j > 0); }
       } else {
-        for (int j = 0; j < ksteps; ++j) { if (leader) mmaTS(d, tmem + 320 + j * 8, desc(bBase + ((j >> 2) & 1) * N * 128 + (j & 3) * 32, 16, 1024, 2), idesc, j > 0); }
+        for (int j = 0; j < ksteps; ++j) { if (leader) mmaTS(d, tmem + j * 8, desc(bBase + ((j >> 2) & 1) * N * 128 + (j & 3) * 32, 16, 1024, 2), idesc, j > 0); }
       }
     }
     if (leader) tcCommit(smemAddr(&bars[0]));
@@ -73,6 +73,23 @@ __global__ void __launch_bounds__(256, 1) bench(int mode, int N, int ksteps, int
     while (!stopFlag) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) { asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(spare + ((off + k * 2048) & 0x7fff)), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
+    }
+  } else if (warp >= 4 && traffic >= 3) {
+    // epilogue-like TMEM traffic: every warp keeps loading (traffic 3) or loading+storing (4) its lane quadrant
+    const uint32_t lb = tmem + (((warp & 3u) * 32u) << 16);
+    uint32_t v[16];
+    uint32_t col = 0;
+    while (!stopFlag) {
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]) : "r"(lb + 160 + col) : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (traffic >= 4) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+          ::"r"(lb + (traffic == 5 ? 80 + (col & 63) : 480 + (col & 15))), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      }
+      col = (col + 16) % 144;
     }
   } else if (warp == 4 && lane == 0 && traffic == 2) {
     uint32_t ph = 0;
@@ -93,10 +110,10 @@ int main() {
   uint8_t* gsrc; cudaMalloc(&gsrc, 1 << 20); cudaMemset(gsrc, 0, 1 << 20);
   cudaFuncSetAttribute(bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   const char* names[] = {"SS noswz", "SS swz128", "TS Bnoswz", "TS Bswz128"};
-  for (int traffic = 0; traffic < 3; ++traffic)
+  for (int traffic : {4, 5})
     for (int mode = 0; mode < 4; ++mode)
-      for (int N : {16, 80, 160, 256}) {
-        const int ksteps = 20, reps = 200;
+      for (int N : {160}) {
+        const int ksteps = 10, reps = 400;
         bench<<<148, 256, 200 * 1024>>>(mode, N, ksteps, reps, traffic, gsrc, out);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("mode %d N %d: %s\n", mode, N, cudaGetErrorString(e)); return 1; }
