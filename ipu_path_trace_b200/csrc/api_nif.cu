@@ -220,7 +220,9 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
       else if (mode == "ss2") { cg = 2; ts = 0; kc = 5; }
       else if (mode == "ts5") { cg = 1; ts = 1; kc = 5; }
       else if (mode == "ts10") { cg = 1; ts = 1; kc = 10; }
-      else return c->fail(B200PT_ERR_INVALID, "B200PT_NIF_MODE must be ss1, ss2, ts5 or ts10");
+      else if (mode == "tp5") { cg = 2; ts = 1; kc = 5; }
+      else if (mode == "tp10") { cg = 2; ts = 1; kc = 10; }
+      else return c->fail(B200PT_ERR_INVALID, "B200PT_NIF_MODE must be ss1, ss2, ts5, ts10, tp5 or tp10");
     }
     NifTcModel& tm = c->tcHost;
     std::vector<uint8_t> stream;

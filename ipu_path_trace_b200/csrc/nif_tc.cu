@@ -186,7 +186,7 @@ __host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden,
   s.stageBytes = (uint32_t)kc * (uint32_t)(H / 2 / cg) * 32u;
   const uint32_t budget = 232448u - 1024u;                       // 227 KB per CTA minus the alignment slack
   uint32_t st = (budget - o) / s.stageBytes;
-  if (!ts) st = cg == 2 ? 8u : 4u;
+  if (!ts) st = cg == 2 ? 8u : 4u;      // the non-TS variants keep their measured configuration
   s.stages = st > 8u ? 8u : st;
   o += s.stages * s.stageBytes;
   s.total = o;
@@ -528,6 +528,7 @@ int nifTcStages(const NifTcModel& m) { return (int)tcLayout(m.H, m.featKSteps, m
 namespace {
 using KernelFn = void (*)(const NifTcModel, const NifIo);
 KernelFn pickKernel(const NifTcModel& m) {
+  if (m.ts && m.cg == 2) return m.kc == 10 ? nif_tc_kernel<2, true, 10> : nif_tc_kernel<2, true, 5>;
   if (m.ts) return m.kc == 10 ? nif_tc_kernel<1, true, 10> : nif_tc_kernel<1, true, 5>;
   return m.cg == 2 ? nif_tc_kernel<2, false, 5> : nif_tc_kernel<1, false, 5>;
 }
