@@ -89,7 +89,19 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     return B200PT_ERR_INVALID;
   }
   c->numSms = prop.multiProcessorCount;
-  if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  {
+    // The NIF stream gets the highest priority so that its persistent blocks are placed first and the
+    // path-tracing blocks of the next wavefront fill the remaining register/thread slots of each SM.
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if ((e = cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithPriority(&c->traceStream, cudaStreamNonBlocking, lo)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    for (int i = 0; i < 2; ++i) {
+      if ((e = cudaEventCreateWithFlags(&c->evQueueFree[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+      if ((e = cudaEventCreateWithFlags(&c->evTraced[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    }
+    if (const char* ov = getenv("B200PT_OVERLAP")) c->overlap = std::atoi(ov) != 0;
+  }
   if ((e = cudaEventCreate(&c->evBegin)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&c->evEnd)) != cudaSuccess) return bail(e, "cudaEventCreate");
 
@@ -110,6 +122,10 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
   if ((e = c->accum.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");
   if ((e = c->qUv.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
   if ((e = c->qThrSlot.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
+  if (c->overlap) {
+    if ((e = c->qUvB.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
+    if ((e = c->qThrSlotB.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
+  }
   if ((e = c->qCount.alloc(4)) != cudaSuccess) return bail(e, "cudaMalloc");
   if ((e = c->stats.alloc(4)) != cudaSuccess) return bail(e, "cudaMalloc");
   const size_t filmN = (size_t)cfg->width * cfg->height * 3;
@@ -131,8 +147,12 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
 void b200pt_destroy(b200pt_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->cfg.device);
+  if (c->traceStream) cudaStreamSynchronize(c->traceStream);
   if (c->stream) cudaStreamSynchronize(c->stream);
   for (cudaEvent_t e : c->evPool) cudaEventDestroy(e);
+  for (int i = 0; i < 2; ++i) { if (c->evQueueFree[i]) cudaEventDestroy(c->evQueueFree[i]); if (c->evTraced[i]) cudaEventDestroy(c->evTraced[i]); }
+  c->qUvB.release(); c->qThrSlotB.release();
+  if (c->traceStream) cudaStreamDestroy(c->traceStream);
   if (c->evBegin) cudaEventDestroy(c->evBegin);
   if (c->evEnd) cudaEventDestroy(c->evEnd);
   c->recStaging.release(); c->pix.release(); c->sampleCount.release(); c->pathLength.release(); c->accum.release();

@@ -39,10 +39,10 @@ std::string tcEligibility(const std::vector<HostLayer>& ls, int nFeat) {
 // Builds the tcgen05 kernel's model: the chunk table and the packed weight stream. Every (layer,
 // N-range, K-range) chunk is the exact shared-memory image of a K-major UMMA B operand, in MMA issue
 // order; for a CTA pair (cg == 2) a chunk is stored as [image of CTA 0's N/2 rows | image of CTA 1's].
-bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200pt_nif_desc& nif, int cg, int ts, int kc, NifTcModel& tm,
+bool buildTcModel(const std::vector<HostLayer>& ls, int nFeat, int E, const b200pt_nif_desc& nif, int cg, int ts, int kc, int mc, NifTcModel& tm,
                   std::vector<uint8_t>& stream) {
   std::memset(&tm, 0, sizeof(tm));
-  tm.cg = cg; tm.ts = ts; tm.kc = kc;
+  tm.cg = cg; tm.ts = ts; tm.kc = kc; tm.mc = mc;
   const int numSlots = ts ? 2 : 3;
   const int numHidden = (int)ls.size() - 1;
   const int H = ls[0].out, NH = H / 2;
@@ -211,22 +211,25 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
     for (int l = 0; l < numHidden; ++l) for (int i = 0; i < H; ++i) bias[(size_t)l * H + i] = ls[l].b[i];
     CU(c, c->tcBias.alloc(bias.size()));
     CU(c, cudaMemcpy(c->tcBias.p, bias.data(), bias.size() * 2, cudaMemcpyHostToDevice));
-    // Kernel variant. Default: activations in tensor memory, 10 K-steps per chunk. B200PT_NIF_MODE =
-    // ss1 | ss2 | ts5 | ts10 selects another one (A/B measurements and the parity tests of each variant).
-    int cg = 1, ts = 1, kc = 10;
+    // Kernel variant. Default (mc10): activations in tensor memory, 10 K-steps per chunk, weight chunks
+    // multicast between the two CTAs of a cluster. B200PT_NIF_MODE = ss1 | ss2 | ts5 | ts10 | tp5 | tp10 |
+    // mc5 | mc10 selects another one (A/B measurements and the parity tests of each variant).
+    int cg = 1, ts = 1, kc = 10, mc = 1;
     if (const char* e = getenv("B200PT_NIF_MODE")) {
       const std::string mode(e);
-      if (mode == "ss1") { cg = 1; ts = 0; kc = 5; }
-      else if (mode == "ss2") { cg = 2; ts = 0; kc = 5; }
-      else if (mode == "ts5") { cg = 1; ts = 1; kc = 5; }
-      else if (mode == "ts10") { cg = 1; ts = 1; kc = 10; }
-      else if (mode == "tp5") { cg = 2; ts = 1; kc = 5; }
-      else if (mode == "tp10") { cg = 2; ts = 1; kc = 10; }
-      else return c->fail(B200PT_ERR_INVALID, "B200PT_NIF_MODE must be ss1, ss2, ts5, ts10, tp5 or tp10");
+      if (mode == "ss1") { cg = 1; ts = 0; kc = 5; mc = 0; }
+      else if (mode == "ss2") { cg = 2; ts = 0; kc = 5; mc = 0; }
+      else if (mode == "ts5") { cg = 1; ts = 1; kc = 5; mc = 0; }
+      else if (mode == "ts10") { cg = 1; ts = 1; kc = 10; mc = 0; }
+      else if (mode == "tp5") { cg = 2; ts = 1; kc = 5; mc = 0; }
+      else if (mode == "tp10") { cg = 2; ts = 1; kc = 10; mc = 0; }
+      else if (mode == "mc10") { cg = 1; ts = 1; kc = 10; mc = 1; }
+      else if (mode == "mc5") { cg = 1; ts = 1; kc = 5; mc = 1; }
+      else return c->fail(B200PT_ERR_INVALID, "B200PT_NIF_MODE must be ss1, ss2, ts5, ts10, tp5, tp10, mc5 or mc10");
     }
     NifTcModel& tm = c->tcHost;
     std::vector<uint8_t> stream;
-    if (!buildTcModel(ls, nFeat, E, *nif, cg, ts, kc, tm, stream)) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; }
+    if (!buildTcModel(ls, nFeat, E, *nif, cg, ts, kc, mc, tm, stream)) { c->tcOk = false; c->tcWhyNot = "too many weight chunks"; }
     else {
       CU(c, c->tcStream.alloc(stream.size()));
       CU(c, cudaMemcpy(c->tcStream.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
@@ -234,8 +237,8 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
       if (nifTcSmemBytes(tm) > 227 * 1024 || nifTcStages(tm) < 2) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; }
       else {
         CU(c, prepareNifTc(tm));
-        c->tcMaxPairs = cg == 2 ? nifTcMaxPairs(tm) : 0;
-        if (cg == 2 && c->tcMaxPairs < 1) { c->tcOk = false; c->tcWhyNot = "no co-resident CTA pairs on this device"; }
+        c->tcMaxPairs = (cg == 2 || mc) ? nifTcMaxPairs(tm) : 0;
+        if ((cg == 2 || mc) && c->tcMaxPairs < 1) { c->tcOk = false; c->tcWhyNot = "no co-resident CTA pairs on this device"; }
       }
     }
   }

@@ -91,25 +91,42 @@ int b200pt_path_trace(b200pt_ctx* c) {
   uint64_t launches = 0;
   int used = 0;
   uint32_t done = 0;
-  while (done < c->samplesPerStep && c->nItems > 0) {
+  // Software pipeline over wavefronts: trace(w) fills queue w & 1 on the trace stream while the NIF
+  // kernel shades queue (w - 1) & 1 on the main stream. The two kernels touch disjoint fields of the
+  // work items (trace: sampleCount/pathLength, NIF: accum). Without overlap everything runs on `stream`.
+  const bool ov = c->overlap;
+  cudaStream_t ts = ov ? c->traceStream : c->stream;
+  if (ov) CU(c, cudaStreamWaitEvent(ts, c->evBegin, 0));       // setup / film work of the main stream comes first
+  for (uint32_t w = 0; done < c->samplesPerStep && c->nItems > 0; ++w) {
     const uint32_t k = std::min(c->samplesPerLaunch, c->samplesPerStep - done);
-    CU(c, cudaMemsetAsync(c->qCount.p, 0, sizeof(uint32_t), c->stream));
-    cudaEvent_t e0 = c->nextEvent(), e1 = c->nextEvent(), e2 = c->nextEvent();
-    if (!e0 || !e1 || !e2) return c->fail(B200PT_ERR_CUDA, "cudaEventCreate failed");
-    const size_t i0 = c->evUsed - 3;
-    CU(c, cudaEventRecord(e0, c->stream));
-    CU(c, launchTraceWavefront(c->scene.p, c->settings, c->pix.p, c->nItems, c->nextSample + done, k, c->qUv.p, c->qThrSlot.p,
-                               c->qCount.p, c->sampleCount.p, c->pathLength.p, c->stats.p, c->stream));
-    CU(c, cudaEventRecord(e1, c->stream));
+    const uint32_t q = ov ? (w & 1u) : 0u;
+    float2* qUv = q ? c->qUvB.p : c->qUv.p;
+    float4* qThr = q ? c->qThrSlotB.p : c->qThrSlot.p;
+    uint32_t* qCount = c->qCount.p + q;
+    cudaEvent_t e0 = c->nextEvent(), e1 = c->nextEvent(), e2 = c->nextEvent(), e3 = c->nextEvent();
+    if (!e0 || !e1 || !e2 || !e3) return c->fail(B200PT_ERR_CUDA, "cudaEventCreate failed");
+    const size_t i0 = c->evUsed - 4;
+    if (ov && w >= 2) CU(c, cudaStreamWaitEvent(ts, c->evQueueFree[q], 0));    // the NIF kernel of wavefront w - 2 has drained this queue
+    CU(c, cudaMemsetAsync(qCount, 0, sizeof(uint32_t), ts));
+    CU(c, cudaEventRecord(e0, ts));
+    CU(c, launchTraceWavefront(c->scene.p, c->settings, c->pix.p, c->nItems, c->nextSample + done, k, qUv, qThr,
+                               qCount, c->sampleCount.p, c->pathLength.p, c->stats.p, ts));
+    CU(c, cudaEventRecord(e1, ts));
+    if (ov) {
+      CU(c, cudaEventRecord(c->evTraced[q], ts));
+      CU(c, cudaStreamWaitEvent(c->stream, c->evTraced[q], 0));
+    }
     NifIo io{};
-    io.uv = c->qUv.p; io.thrSlot = c->qThrSlot.p; io.count = c->qCount.p;
+    io.uv = qUv; io.thrSlot = qThr; io.count = qCount;
     io.countHost = (uint32_t)std::min<size_t>((size_t)c->nItems * k, 0xffffffffu);
     io.bgrOut = nullptr; io.accum = reinterpret_cast<float*>(c->accum.p);
+    CU(c, cudaEventRecord(e2, c->stream));
     rc = launchNif(c, io, B200PT_NIF_AUTO, &used);
     if (rc) return rc;
-    CU(c, cudaEventRecord(e2, c->stream));
+    CU(c, cudaEventRecord(e3, c->stream));
+    if (ov) CU(c, cudaEventRecord(c->evQueueFree[q], c->stream));
     c->spans.push_back({i0, i0 + 1, 0});
-    c->spans.push_back({i0 + 1, i0 + 2, 1});
+    c->spans.push_back({i0 + 2, i0 + 3, 1});
     launches += 2;
     done += k;
   }

@@ -43,7 +43,12 @@ struct b200pt_ctx {
   std::string error;
   int numSms = 0;
   cudaStream_t stream = nullptr;
+  // Second stream: the path-tracing kernel of wavefront w+1 runs beside the NIF kernel of wavefront w
+  // (the NIF kernel leaves registers and shared memory for one trace block per SM).
+  cudaStream_t traceStream = nullptr;
+  bool overlap = true;
   cudaEvent_t evBegin = nullptr, evEnd = nullptr;
+  cudaEvent_t evQueueFree[2] = {nullptr, nullptr}, evTraced[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> evPool;       // per-launch timing events of the last path_trace
   size_t evUsed = 0;
   struct Span { size_t a, b; int kind; };  // kind 0 trace, 1 nif
@@ -62,9 +67,9 @@ struct b200pt_ctx {
   DevBuf<uint32_t> pix, sampleCount, pathLength;
   DevBuf<float4> accum;
   // wavefront queue
-  DevBuf<float2> qUv;
-  DevBuf<float4> qThrSlot;
-  DevBuf<uint32_t> qCount;
+  DevBuf<float2> qUv, qUvB;             // two queues: one being filled while the other is shaded
+  DevBuf<float4> qThrSlot, qThrSlotB;
+  DevBuf<uint32_t> qCount;               // [0], [1]: row counts of the two queues
   DevBuf<unsigned long long> stats;
   // film
   DevBuf<SceneSoA> scene;

@@ -71,7 +71,8 @@ struct NifTcModel {
   int relu[kMaxNifLayers];
   int outC, finalRelu;
   int slotUses[3];             // jobs per tile on each accumulator slot
-  int cg, ts, kc;              // kernel variant: CTAs per MMA group, activations in TMEM, K-steps per chunk
+  int cg, ts, kc, mc;          // kernel variant: CTAs per MMA group, activations in TMEM, K-steps per chunk,
+                               // weight chunks multicast between the two CTAs of a cluster
   const uint8_t* wStream;      // packed chunks (device)
   const __half* bias;          // [numHidden][H] (device; zeros where a layer has no bias)
   float bOut[4];

@@ -23,6 +23,7 @@
 // that every MMA that read a column range has completed before the epilogue that overwrites it
 // is released.
 #include "nif_common.cuh"
+#include <cstdlib>
 
 namespace b2 {
 
@@ -77,11 +78,21 @@ __device__ __forceinline__ void bulkCopyG2S(uint32_t dst, const void* src, uint3
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// Same, delivered to the same CTA-relative offsets (data and barrier) of every CTA in ctaMask.
+__device__ __forceinline__ void bulkCopyG2SMulticast(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint16_t ctaMask) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(ctaMask) : "memory");
+}
 __device__ __forceinline__ void fenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fenceBarrierInit() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void tcFenceBefore() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcFenceAfter() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // MMA-completion arrive. CG == 2: the arrive is multicast to the barrier at this offset in both CTAs.
+// MC: single-CTA MMAs whose completion is announced to both CTAs of a weight-sharing cluster.
+__device__ __forceinline__ void tcCommitBoth(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
 template <int CG>
 __device__ __forceinline__ void tcCommit(uint32_t bar) {
   if (CG == 2)
@@ -208,7 +219,11 @@ enum { BAR_W_FULL = 0, BAR_W_EMPTY = 8, BAR_PEER_W_FULL = 16, BAR_FEAT_FULL = 24
 // memory, and the 80 KB it occupied go to the weight ring. TMEM then holds activations (H/2 columns),
 // two accumulator slots (one per half-job) and the output accumulator.
 // KC: K-steps per weight chunk (= MMAs per ring stage).
-template <int CG, bool TS, int KC>
+// MC (with CG = 1): two CTAs of a cluster run independent M = 128 pipelines on their own tiles but share
+// the weight stream: each CTA fetches half of every chunk and multicasts it into the ring of both, so
+// L2 -> SM weight traffic per row halves without the cross-CTA MMA. A ring stage is free once the MMAs
+// of BOTH CTAs have read it (multicast commit, barrier count 2).
+template <int CG, bool TS, int KC, bool MC>
 __global__ void __launch_bounds__(kTcThreads, 1)
 nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // The model (incl. the chunk table) is a kernel parameter: the MMA and producer warps read it
@@ -225,7 +240,9 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   const uint32_t outCol = 3u * (uint32_t)NH;            // output accumulator (16 columns)
   const uint32_t sbase = smemAddr(smem);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  const uint32_t rank = (CG == 2) ? clusterCtaRank() : 0u;
+  static_assert(!(MC && CG == 2), "weight multicast is the single-CTA-MMA alternative to the CTA pair");
+  constexpr uint32_t CL = (CG == 2 || MC) ? 2u : 1u;     // CTAs per cluster = tiles per work unit
+  const uint32_t rank = (CL == 2) ? clusterCtaRank() : 0u;
   const uint32_t barBase = sbase + L.bars;
   auto bar = [&](int i) { return barBase + 8u * (uint32_t)i; };
   // arrival on a barrier that gates the MMA issuer: lives in the rank-0 CTA
@@ -237,8 +254,8 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   const uint32_t numTiles = (count + kTcRows - 1) / kTcRows;
   // work unit = CG consecutive tiles (one per CTA of the group); both CTAs of a pair run the same
   // number of units, a tile index past the end is all padding rows
-  const uint32_t numUnits = (numTiles + CG - 1) / CG;
-  const uint32_t unit0 = blockIdx.x / CG, unitStride = gridDim.x / CG;
+  const uint32_t numUnits = (numTiles + CL - 1) / CL;
+  const uint32_t unit0 = blockIdx.x / CL, unitStride = gridDim.x / CL;
 
   // ---- one-time setup ----
   {
@@ -248,7 +265,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     for (int i = threadIdx.x; i < numHidden * H / 2; i += kTcThreads) sb[i] = gb[i];
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { mbarInit(bar(BAR_W_FULL + s), 1); mbarInit(bar(BAR_W_EMPTY + s), 1); mbarInit(bar(BAR_PEER_W_FULL + s), 1); }
+    for (int s = 0; s < kStages; ++s) { mbarInit(bar(BAR_W_FULL + s), 1); mbarInit(bar(BAR_W_EMPTY + s), MC ? 2 : 1); mbarInit(bar(BAR_PEER_W_FULL + s), 1); }
     for (int b = 0; b < 2; ++b) {
       mbarInit(bar(BAR_FEAT_FULL + b), CG * kEncodeWarps);
       mbarInit(bar(BAR_FEAT_EMPTY + b), 1);
@@ -270,7 +287,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   }
   tcFenceBefore();
   __syncthreads();
-  if (CG == 2) clusterSync();          // the peer's barriers are initialised before anyone signals them
+  if (CL == 2) clusterSync();          // the peer's barriers are initialised before anyone signals them
   tcFenceAfter();
   const uint32_t tmemBase = *reinterpret_cast<volatile uint32_t*>(smem + L.tmemSlot);
   const uint32_t stageBytes = L.stageBytes;
@@ -285,8 +302,16 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         const uint32_t bytes = (uint32_t)m.chunks[c].bytes16 * (16u / CG);      // this CTA's share of the chunk
         { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_W_EMPTY + stage), phase ^ 1u); PROF_ADD(qEmpty, t0); }
         if (leader) {
-          mbarArriveExpectTx(bar(BAR_W_FULL + stage), bytes);
-          bulkCopyG2S(sbase + L.ring + stage * stageBytes, m.wStream + m.chunks[c].offset + rank * bytes, bytes, bar(BAR_W_FULL + stage));
+          if (MC) {
+            // my half of the chunk goes to both rings; the peer sends the other half
+            const uint32_t half = bytes / 2u;
+            mbarArriveExpectTx(bar(BAR_W_FULL + stage), bytes);
+            bulkCopyG2SMulticast(sbase + L.ring + stage * stageBytes + rank * half, m.wStream + m.chunks[c].offset + rank * half, half,
+                                 bar(BAR_W_FULL + stage), (uint16_t)3);
+          } else {
+            mbarArriveExpectTx(bar(BAR_W_FULL + stage), bytes);
+            bulkCopyG2S(sbase + L.ring + stage * stageBytes, m.wStream + m.chunks[c].offset + rank * bytes, bytes, bar(BAR_W_FULL + stage));
+          }
         }
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
@@ -295,7 +320,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     if (lane == 0) { unsigned long long* p = g_tcProf + blockIdx.x * 16 + 13; p[0] = qEmpty; p[1] = clock64() - qStart; }
 #endif
     __syncwarp();
-  } else if (warp == 1 && rank != 0) {
+  } else if (warp == 1 && CG == 2 && rank != 0) {
     // ================= weight-arrival relay (peer CTA of a pair) =================
     // cp.async.bulk can only signal a barrier of its destination CTA, so this warp forwards
     // "my half of the stage has landed" to the issuer's barrier in the rank-0 CTA.
@@ -311,15 +336,17 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   } else if (warp == 1) {
     // ================= MMA issuer (converged warp, one elected lane issues) =================
     const bool leader = electOne();
-    const uint32_t actLo = ((sbase + L.act) >> 4);
-    const uint32_t ringLo = ((sbase + L.ring) >> 4);
+    // Descriptor start addresses are 14-bit fields of (address & 0x3FFFF) >> 4: in a cluster launch the
+    // shared-window address of an odd-ranked CTA carries the rank above bit 18 and must be masked off.
+    const uint32_t actLo = (((sbase + L.act) & 0x3FFFFu) >> 4);
+    const uint32_t ringLo = (((sbase + L.ring) & 0x3FFFFu) >> 4);
     uint32_t stage = 0, phase = 0;
     uint32_t actUse0 = 0, actUse1 = 0;     // completed waits on act_ready[part]
     uint32_t it = 0;
     long long pFeat = 0, pAcc = 0, pAct = 0, pW = 0, pOutE = 0, pPeer = 0, pIssue = 0; const long long pStart = PROF_T(); (void)pStart;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       const uint32_t fb = it & 1u;
-      const uint32_t featLo = ((sbase + L.feat[fb]) >> 4);
+      const uint32_t featLo = (((sbase + L.feat[fb]) & 0x3FFFFu) >> 4);
       { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_FEAT_FULL + fb), (it >> 1) & 1u); PROF_ADD(pFeat, t0); }
       for (int c = 0; c < numChunks; ++c) {
         const NifTcChunk& ch = m.chunks[c];
@@ -373,7 +400,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           }
         }
         if (leader) {
-          tcCommit<CG>(bar(BAR_W_EMPTY + stage));
+          if (MC) tcCommitBoth(bar(BAR_W_EMPTY + stage)); else tcCommit<CG>(bar(BAR_W_EMPTY + stage));
           if (flags & kChLast) tcCommit<CG>(bar(isOut ? BAR_OUT_FULL : BAR_ACC_FULL + buf));
           if (flags & kChLastFeatUse) tcCommit<CG>(bar(BAR_FEAT_EMPTY + fb));
         }
@@ -392,7 +419,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     uint32_t it = 0;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
       const uint32_t fb = it & 1u;
-      const uint32_t row = (unit * CG + rank) * kTcRows + r;
+      const uint32_t row = (unit * CL + rank) * kTcRows + r;
       float2 uv = make_float2(0.f, 0.f);
       if (row < count) uv = io.uv[row];
       __half f[kMaxFeatures];
@@ -487,7 +514,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         tcFenceBefore();
         __syncwarp();
         if (lane == 0) arriveIssuer(BAR_OUT_EMPTY);
-        const uint32_t row = (unit * CG + rank) * kTcRows + r;
+        const uint32_t row = (unit * CL + rank) * kTcRows + r;
         if (row < count) {
           float out[3];
 #pragma unroll
@@ -512,7 +539,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   // ---- teardown ----
   tcFenceBefore();
   __syncthreads();
-  if (CG == 2) clusterSync();        // the peer may still be signalling barriers here / reading its TMEM half
+  if (CL == 2) clusterSync();        // the peer may still be signalling barriers here / reading its TMEM half
   tcFenceAfter();
   if (warp == 1) {
     if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "r"(kTmemCols) : "memory");
@@ -528,9 +555,10 @@ int nifTcStages(const NifTcModel& m) { return (int)tcLayout(m.H, m.featKSteps, m
 namespace {
 using KernelFn = void (*)(const NifTcModel, const NifIo);
 KernelFn pickKernel(const NifTcModel& m) {
-  if (m.ts && m.cg == 2) return m.kc == 10 ? nif_tc_kernel<2, true, 10> : nif_tc_kernel<2, true, 5>;
-  if (m.ts) return m.kc == 10 ? nif_tc_kernel<1, true, 10> : nif_tc_kernel<1, true, 5>;
-  return m.cg == 2 ? nif_tc_kernel<2, false, 5> : nif_tc_kernel<1, false, 5>;
+  if (m.mc) return m.kc == 10 ? nif_tc_kernel<1, true, 10, true> : nif_tc_kernel<1, true, 5, true>;
+  if (m.ts && m.cg == 2) return m.kc == 10 ? nif_tc_kernel<2, true, 10, false> : nif_tc_kernel<2, true, 5, false>;
+  if (m.ts) return m.kc == 10 ? nif_tc_kernel<1, true, 10, false> : nif_tc_kernel<1, true, 5, false>;
+  return m.cg == 2 ? nif_tc_kernel<2, false, 5, false> : nif_tc_kernel<1, false, 5, false>;
 }
 } // namespace
 
@@ -570,7 +598,7 @@ cudaError_t launchNifTc(const NifTcModel& model, const NifIo& io, int numSms, in
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr; cfg.numAttrs = 0;
-  if (model.cg == 2) {
+  if (model.cg == 2 || model.mc) {
     const uint32_t pairsMax = (tilesMax + 1) / 2;
     grid = 2 * (pairsMax < (uint32_t)maxPairs ? pairsMax : (uint32_t)maxPairs);
     attr[0].id = cudaLaunchAttributeClusterDimension;

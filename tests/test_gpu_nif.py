@@ -97,3 +97,26 @@ def test_linear_output_no_tone_map(lib_built, O, orc):
     got = t.nif_infer(u, v)
     np.testing.assert_allclose(got, orc.nif_forward(nif, u, v, mode=0), atol=1e-2)
     t.close()
+
+
+@pytest.mark.parametrize("mode", ["ss1", "ss2", "ts5", "ts10", "tp5", "tp10", "mc5", "mc10"])
+def test_every_kernel_variant_matches_oracle(lib_built, nif_model, orc, oracle_nif, mode, monkeypatch):
+    """B200PT_NIF_MODE selects the tcgen05 kernel variant at init_nif_weights time (activations in shared
+    or tensor memory, single CTA / CTA pair / weight multicast between two CTAs, 5 or 10 K-steps per chunk).
+    Every variant must give the default variant's result bit for bit and match the oracle."""
+    n = 2 * 148 * 128 + 77          # more than one tile per CTA, odd tile count, ragged last tile
+    u, v = _uv(n, 31)
+    monkeypatch.delenv("B200PT_NIF_MODE", raising=False)
+    t0 = lib_built.PathTracer(16, 16)
+    t0.init_nif_weights(nif_model)
+    base = t0.nif_infer(u, v, lib_built.NIF_TCGEN05)
+    t0.close()
+    monkeypatch.setenv("B200PT_NIF_MODE", mode)
+    t = lib_built.PathTracer(16, 16)
+    t.init_nif_weights(nif_model)
+    got = t.nif_infer(u, v, lib_built.NIF_TCGEN05)
+    t.close()
+    assert np.array_equal(got, base)
+    sel = np.random.default_rng(2).choice(n, 2048, replace=False)
+    want = orc.nif_forward(oracle_nif, u[sel], v[sel], mode=0)
+    assert np.abs(np.log(got[sel]) - np.log(want)).max() < 1e-2
