@@ -186,8 +186,11 @@ __host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden,
   TcSmem s;
   uint32_t o = 0;
   s.act = o; if (!ts) o += (uint32_t)H * kTcRows * 2;
+  // With activations in tensor memory one feature buffer is enough: its last reader (the skip-concat layer)
+  // is done half a tile before the next tile's first layer needs the new features, and the 12 KB buy the
+  // weight ring a fourth stage.
   s.feat[0] = o; o += (uint32_t)featKSteps * 4096;
-  s.feat[1] = o; o += (uint32_t)featKSteps * 4096;
+  s.feat[1] = ts ? s.feat[0] : o; if (!ts) o += (uint32_t)featKSteps * 4096;
   s.bias = o; o += (uint32_t)numHidden * H * 2;
   o = (o + 15u) & ~15u;
   s.bars = o; o += 48 * 8;
@@ -345,9 +348,9 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     uint32_t it = 0;
     long long pFeat = 0, pAcc = 0, pAct = 0, pW = 0, pOutE = 0, pPeer = 0, pIssue = 0; const long long pStart = PROF_T(); (void)pStart;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
-      const uint32_t fb = it & 1u;
+      const uint32_t fb = TS ? 0u : (it & 1u), fpar = TS ? (it & 1u) : ((it >> 1) & 1u);
       const uint32_t featLo = (((sbase + L.feat[fb]) & 0x3FFFFu) >> 4);
-      { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_FEAT_FULL + fb), (it >> 1) & 1u); PROF_ADD(pFeat, t0); }
+      { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_FEAT_FULL + fb), fpar); PROF_ADD(pFeat, t0); }
       for (int c = 0; c < numChunks; ++c) {
         const NifTcChunk& ch = m.chunks[c];
         const uint32_t ksteps = ch.ksteps, n8 = ch.n8, flags = ch.flags, waitAct = ch.waitAct;
@@ -418,7 +421,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     const int E = m.embeddingDim, featCores = m.featKSteps * 2;
     uint32_t it = 0;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
-      const uint32_t fb = it & 1u;
+      const uint32_t fb = TS ? 0u : (it & 1u), fpar = TS ? (it & 1u) : ((it >> 1) & 1u);
       const uint32_t row = (unit * CL + rank) * kTcRows + r;
       float2 uv = make_float2(0.f, 0.f);
       if (row < count) uv = io.uv[row];
@@ -427,7 +430,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       for (int k = 0; k < kMaxFeatures; ++k) f[k] = __float2half_rn(0.f);
       nifEncode(uv.x, uv.y, E, [&](int k, __half v) { f[k] = v; });
       // wait until the MMAs of the unit that last used this buffer are done with it
-      mbarWait<CG>(bar(BAR_FEAT_EMPTY + fb), ((it >> 1) & 1u) ^ 1u);
+      mbarWait<CG>(bar(BAR_FEAT_EMPTY + fb), fpar ^ 1u);
       unsigned char* fbuf = smem + L.feat[fb];
       for (int kc = 0; kc < featCores; ++kc) {
         uint4 pk;
