@@ -1,0 +1,281 @@
+#include "PathTracerApp.hpp"
+
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <chrono>
+#include <cmath>
+#include <sstream>
+#include <stdexcept>
+
+#include "AsyncTask.hpp"
+#include "logging.hpp"
+
+std::size_t roundSamplesPerPixel(std::size_t samplesPerPixel, std::size_t samplesPerStep) {
+  if (samplesPerPixel % samplesPerStep) {
+    samplesPerPixel += samplesPerStep - (samplesPerPixel % samplesPerStep);
+    logging::info("Rounding SPP to next multiple of {}  (Rounded SPP :=  {})", samplesPerStep, samplesPerPixel);
+  }
+  return samplesPerPixel;
+}
+
+struct PathTracerApp::Gpu {
+  int device = 0;
+  b200pt_ctx* ctx = nullptr;
+  float* staging = nullptr;          // full-frame film copy for the gather (device memory)
+  float* reduced = nullptr;          // gather result (root only)
+  cudaStream_t stream = nullptr;
+  ~Gpu() {
+    if (ctx) b200pt_destroy(ctx);
+    cudaSetDevice(device);
+    if (staging) cudaFree(staging);
+    if (reduced) cudaFree(reduced);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+struct PathTracerApp::FilmGather {
+  std::vector<ncclComm_t> comms;
+  ~FilmGather() { for (auto c : comms) if (c) ncclCommDestroy(c); }
+};
+
+PathTracerApp::PathTracerApp() {}
+PathTracerApp::~PathTracerApp() { gather.reset(); gpus.clear(); }
+
+void PathTracerApp::check(int rc, Gpu& g, const char* what) {
+  if (rc == B200PT_OK) return;
+  std::stringstream ss;
+  ss << what << " failed on GPU " << g.device << " (" << rc << "): " << b200pt_last_error(g.ctx);
+  throw std::runtime_error(ss.str());
+}
+
+void PathTracerApp::init(const Options& options) {
+  args = &options;
+  samplesPerPixel = options.u32("samples");
+  samplesPerStep = options.u32("samples-per-step");
+  if (samplesPerStep == 0) throw std::runtime_error("samples-per-step must be positive");
+  samplesPerPixel = roundSamplesPerPixel(samplesPerPixel, samplesPerStep);
+  for (const char* ignored : {"model", "save-exe", "load-exe", "compile-only", "defer-attach", "codelet-path", "partials-type", "available-memory-proportion"})
+    if (options.given(ignored)) logging::warn("Option --{} configures the Poplar graph of the reference and has no effect here.", ignored);
+  if (options.u32("ui-port") != 0) logging::warn("The remote user interface (--ui-port) is not part of this build; rendering head-less.");
+  if (!loadNifModels(options.str("assets"))) throw std::runtime_error("Could not load NIF model.");
+}
+
+bool PathTracerApp::loadNifModels(const std::string& assetPath) {
+  try {
+    nif.reset(new NifModelData(assetPath, args->flag("synthetic-weights")));
+  } catch (std::exception& e) {
+    logging::error("Could not load NIF model from '{}'. Exception: {}", assetPath, e.what());
+    return false;
+  }
+  return true;
+}
+
+void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, std::size_t itemsPerGpu) {
+  const std::size_t numGpus = args->u64("ipus");
+  std::vector<int> devices;
+  if (args->given("devices")) {
+    std::stringstream ss(args->str("devices"));
+    std::string tok;
+    while (std::getline(ss, tok, ',')) devices.push_back(std::atoi(tok.c_str()));
+    if (devices.size() != numGpus) throw std::runtime_error("--devices must list exactly --ipus ordinals");
+  } else {
+    for (std::size_t g = 0; g < numGpus; ++g) devices.push_back((int)g);
+  }
+  const std::string aaName = args->str("aa-noise-type");
+  int aaType;
+  if (aaName == "normal") aaType = B200PT_AA_NORMAL;
+  else if (aaName == "uniform") aaType = B200PT_AA_UNIFORM;
+  else if (aaName == "truncated-normal") aaType = B200PT_AA_TRUNCATED_NORMAL;
+  else throw std::runtime_error("Invalid AA noise type: " + aaName);       // PathTracerApp.cpp:43-45
+
+  // --max-nif-batch-size bounded the serialised NIF batch on the IPU; here it sizes the escaped-ray
+  // wavefront: whole samples of every pixel of the GPU per launch (0 = let the library choose).
+  std::uint32_t samplesPerLaunch = 0;
+  if (args->given("max-nif-batch-size") && args->u64("max-nif-batch-size") > 0)
+    samplesPerLaunch = (std::uint32_t)std::max<std::uint64_t>(1, args->u64("max-nif-batch-size") / std::max<std::size_t>(1, itemsPerGpu));
+
+  for (std::size_t g = 0; g < numGpus; ++g) {
+    std::unique_ptr<Gpu> gpu(new Gpu());
+    gpu->device = devices[g];
+    b200pt_config cfg{};
+    cfg.struct_size = sizeof(cfg);
+    cfg.device = devices[g];
+    cfg.width = width; cfg.height = height;
+    cfg.max_path_length = args->u32("max-path-length");
+    cfg.roulette_depth = args->u32("roulette-depth");
+    cfg.stop_prob = args->f32("stop-prob");
+    cfg.refractive_index = args->f32("refractive-index");
+    cfg.aa_noise_type = aaType;
+    cfg.max_worklist = (std::uint32_t)itemsPerGpu;
+    cfg.samples_per_launch = samplesPerLaunch;
+    cfg.nif_impl = B200PT_NIF_AUTO;
+    const int rc = b200pt_create(&cfg, &gpu->ctx);
+    if (rc != B200PT_OK) {
+      std::stringstream ss;
+      ss << "Could not create a render context on GPU " << devices[g] << " (" << rc << "): " << b200pt_last_error(nullptr);
+      throw std::runtime_error(ss.str());
+    }
+    gpus.push_back(std::move(gpu));
+  }
+  logging::info("Created {} GPU context(s): {}", gpus.size(), b200pt_version());
+}
+
+// One gather of the per-GPU films per save interval. Every GPU holds a full-frame film that is zero
+// outside its own pixels, so the gather is an exact sum: ncclReduce to GPU 0 over NVLink, one D->H copy.
+void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
+  const std::size_t n = film.width() * film.height() * 3;
+  if (gpus.size() == 1) {
+    std::vector<float> host(n);
+    check(b200pt_film_read(gpus[0]->ctx, host.data(), 1.f), *gpus[0], "film_read");
+    film.setHdr(host.data());
+    return;
+  }
+  auto cuda = [](cudaError_t e, const char* what) { if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e)); };
+  auto nccl = [](ncclResult_t r, const char* what) { if (r != ncclSuccess) throw std::runtime_error(std::string(what) + ": " + ncclGetErrorString(r)); };
+  if (!gather) {
+    gather.reset(new FilmGather());
+    std::vector<int> devs;
+    for (auto& g : gpus) devs.push_back(g->device);
+    gather->comms.assign(gpus.size(), nullptr);
+    nccl(ncclCommInitAll(gather->comms.data(), (int)gpus.size(), devs.data()), "ncclCommInitAll");
+    for (auto& g : gpus) {
+      cuda(cudaSetDevice(g->device), "cudaSetDevice");
+      cuda(cudaMalloc(&g->staging, n * sizeof(float)), "cudaMalloc");
+      cuda(cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    }
+    cuda(cudaSetDevice(gpus[0]->device), "cudaSetDevice");
+    cuda(cudaMalloc(&gpus[0]->reduced, n * sizeof(float)), "cudaMalloc");
+  }
+  for (auto& g : gpus) check(b200pt_film_read_device(g->ctx, g->staging, 1.f), *g, "film_read_device");   // synchronises the context
+  nccl(ncclGroupStart(), "ncclGroupStart");
+  for (std::size_t i = 0; i < gpus.size(); ++i)
+    nccl(ncclReduce(gpus[i]->staging, gpus[0]->reduced, n, ncclFloat, ncclSum, 0, gather->comms[i], gpus[i]->stream), "ncclReduce");
+  nccl(ncclGroupEnd(), "ncclGroupEnd");
+  for (auto& g : gpus) { cuda(cudaSetDevice(g->device), "cudaSetDevice"); cuda(cudaStreamSynchronize(g->stream), "cudaStreamSynchronize"); }
+  std::vector<float> host(n);
+  cuda(cudaSetDevice(gpus[0]->device), "cudaSetDevice");
+  cuda(cudaMemcpy(host.data(), gpus[0]->reduced, n * sizeof(float), cudaMemcpyDeviceToHost), "cudaMemcpy");
+  film.setHdr(host.data());
+}
+
+RenderSummary PathTracerApp::execute() {
+  const auto imageWidth = args->u32("width");
+  const auto imageHeight = args->u32("height");
+  const auto seed = args->u64("seed");
+  const auto antiAliasingScale = args->f32("aa-noise-scale");
+  const float fieldOfView = args->f32("fov") * (float)(M_PI / 180.0);
+  const auto exposure = args->f32("exposure");
+  const auto gamma = args->f32("gamma");
+  const auto fileName = args->str("outfile");
+  const auto loadBalanceEnabled = args->flag("enable-load-balancing");
+  const auto saveInterval = std::max<std::uint32_t>(1, args->u32("save-interval"));
+  const bool hostFilm = args->flag("host-film");
+  const auto steps = samplesPerPixel / samplesPerStep;
+  const float degrees = args->f32("env-map-rotation");
+  const float radians = (degrees / 360.f) * (float)(2.0 * M_PI);
+  if (imageWidth == 0 || imageHeight == 0 || imageWidth > 65535 || imageHeight > 65535)
+    throw std::runtime_error("Image width and height must be in 1..65535 (TraceRecord coordinates are 16 bit).");
+  if (loadBalanceEnabled && !hostFilm) logging::warn("--enable-load-balancing re-deals work items between steps and needs the per-step record stream: enabling --host-film.");
+  const bool recordStream = hostFilm || loadBalanceEnabled;
+
+  auto startTime = std::chrono::steady_clock::now();
+
+  // Build the tracing jobs (initialiseState, PathTracerApp.cpp:484-497): pixel tiles dealt to GPUs.
+  auto jobs = createTracingJobs(imageWidth, imageHeight, args->u64("ipus"));
+  logging::info("Created worklists for {} GPUs ({} work items each)", jobs.size(), jobs.front().size());
+  LoadBalancer work(jobs);
+  AccumulatedImage film(imageWidth, imageHeight);
+  createContexts(imageWidth, imageHeight, work.jobSize());
+
+  // init_nif_weights, init_render_settings (:610-611)
+  b200pt_nif_desc desc = nif->descriptor();
+  for (auto& g : gpus) {
+    check(b200pt_upload_nif(g->ctx, &desc), *g, "init_nif_weights");
+    check(b200pt_set_render_settings(g->ctx, seed, antiAliasingScale, fieldOfView, radians, samplesPerStep), *g, "init_render_settings");
+  }
+  if (!recordStream)
+    for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
+
+  AsyncTask hostProcessing;
+  RenderSummary summary;
+  summary.steps = steps;
+  summary.samplesPerPixel = samplesPerPixel;
+  logging::info("Render started");
+  std::size_t totalRays = 0;
+
+  for (std::size_t step = 1; step <= steps; ++step) {
+    auto loopStartTime = std::chrono::steady_clock::now();
+
+    // Run path tracing on the GPUs (setup / path_trace / read_results, :690-694). Results go into the
+    // active buffer whilst the async host task processes the last result from the inactive buffer.
+    if (recordStream)
+      for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
+    for (auto& g : gpus) check(b200pt_path_trace(g->ctx), *g, "path_trace");     // asynchronous: all GPUs run concurrently
+    std::size_t stepRays = 0;
+    for (std::size_t g = 0; g < gpus.size(); ++g) {
+      b200pt_counters ctr{};
+      if (recordStream) check(b200pt_read_results(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize(), &ctr), *gpus[g], "read_results");
+      else {
+        check(b200pt_film_accumulate(gpus[g]->ctx), *gpus[g], "film_accumulate");
+        check(b200pt_get_counters(gpus[g]->ctx, &ctr), *gpus[g], "sync");
+      }
+      summary.paths += ctr.paths; summary.escaped += ctr.escaped; summary.rays += ctr.path_segments;
+      summary.traceMs += ctr.trace_ms; summary.nifMs += ctr.nif_ms; summary.deviceMs = std::max(summary.deviceMs, 0.0) + ctr.total_ms / gpus.size();
+      stepRays += ctr.path_segments;
+      logging::debug("GPU {}: path-trace {} ms, NIF {} ms, total {} ms", gpus[g]->device, ctr.trace_ms, ctr.nif_ms, ctr.total_ms);
+    }
+
+    // Wait for completion of previous async task before starting the next (:702-706):
+    hostProcessing.waitForCompletion();
+
+    const bool saveNow = (step % saveInterval == 0) || step == steps;
+    if (recordStream) {
+      // Swap the worklist buffers; the host thread processes the results in the now inactive list.
+      work.getWork().swap();
+      work.getWork().active() = work.getWork().inactive();     // same items, accumulators cleared below for the GPU
+      work.clearActiveAccumulators();
+      hostProcessing.run([&, step, saveNow]() {
+        film.accumulate(work.getWork().inactive());
+        if (loadBalanceEnabled && step > 1) work.allocateWorkByPathLength();
+        totalRays = work.clearInactiveAccumulators();
+        if (saveNow) {
+          film.saveImages(fileName, step, exposure, gamma);
+          logging::info("Saved images at step {}", step);
+        }
+      });
+    } else {
+      totalRays = stepRays;
+      if (saveNow) {
+        // one gather per save interval; encoding and writing the files overlaps the next steps
+        gatherDeviceFilm(film);
+        hostProcessing.run([&, step]() {
+          film.saveImages(fileName, step, exposure, gamma);
+          logging::info("Saved images at step {}", step);
+        });
+      }
+    }
+
+    auto loopEndTime = std::chrono::steady_clock::now();
+    auto secs = std::chrono::duration<double>(loopEndTime - loopStartTime).count();
+    const double pixelSamplesPerStep = (double)imageWidth * imageHeight * samplesPerStep;
+    logging::info("Completed render step {}/{} in {} seconds (Samples/sec {}) (Rays/sec {})", step, steps, secs, pixelSamplesPerStep / secs,
+                  (recordStream ? totalRays : stepRays) / secs);
+  }
+
+  hostProcessing.waitForCompletion();
+  if (recordStream && loadBalanceEnabled) {
+    // the inactive list was re-dealt for a step that never ran: nothing to do, the film is complete
+  }
+
+  auto endTime = std::chrono::steady_clock::now();
+  summary.elapsedSecs = std::chrono::duration<double>(endTime - startTime).count();
+  logging::info("Render finished: {} seconds", summary.elapsedSecs);
+  const double pixelsPerFrame = (double)imageWidth * imageHeight;
+  summary.samplesPerSec = (pixelsPerFrame / summary.elapsedSecs) * (double)samplesPerPixel;
+  logging::info("Samples/sec: {}", summary.samplesPerSec);
+  logging::info("Samples/sec/GPU: {}", summary.samplesPerSec / gpus.size());
+  if (summary.paths) logging::info("Escaped-ray fraction: {} ; device time per step: path-trace {} ms, NIF {} ms", (double)summary.escaped / summary.paths,
+                                   summary.traceMs / steps / gpus.size(), summary.nifMs / steps / gpus.size());
+  return summary;
+}

@@ -1,0 +1,325 @@
+"""CPU tests of the C++ host (host/): option parser, work lists, film, PNG/EXR writers, NIF asset loaders
+and the HDF5 subset reader, through libb200pt_host.so (no GPU code inside). References:
+src/main.cpp:8-66, src/PathTracerApp.cpp:19-27,794-830, src/LoadBalancer.cpp, src/AccumulatedImage.cpp,
+src/neural_networks/NifMetaData.cpp, src/keras/Hdf5Model.cpp."""
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "host")
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+METADATA = {   # the fields of the shipped assets.extra/nif_metadata.txt the loader reads (NifMetaData.cpp:19-64)
+    "embedding_dimension": 12, "embedding_sigma": 2.0,
+    "encode_params": {"eps": 1e-08, "log_tone_map": True, "max": 3.4299468994140625,
+                      "mean": [-2.3514461517333984, -2.2660605907440186, -1.9648972749710083], "transfer_function": "log"},
+    "keras_model": "/x/urban_alley_01_4k_fp16_yuv", "name": "/x/hdris/urban_alley_01_4k.exr",
+    "original_image_shape": [2048, 4096, 3],
+    "train_command": ["train_nif.py", "--fp16", "--layer-count", "6", "--layer-size", "320", "--embedding-dimension", "12"],
+}
+
+
+@pytest.fixture(scope="session")
+def host():
+    subprocess.run(["make", "-C", HOST, "libb200pt_host.so"], check=True, capture_output=True)
+    lib = C.CDLL(os.path.join(HOST, "libb200pt_host.so"))
+    lib.b200host_last_error.restype = C.c_char_p
+    lib.b200host_create_jobs.restype = C.c_long
+    lib.b200host_balance.restype = C.c_long
+    lib.b200host_round_spp.restype = C.c_size_t
+    lib.b200host_round_spp.argtypes = [C.c_size_t, C.c_size_t]
+    return lib
+
+
+def _opts(host, *argv):
+    args = (C.c_char_p * (len(argv) + 1))(b"b200_path_trace", *[a.encode() for a in argv])
+    out = C.create_string_buffer(1 << 14)
+    rc = host.b200host_parse_options(len(argv) + 1, args, out, len(out))
+    if rc:
+        raise RuntimeError(host.b200host_last_error().decode())
+    return dict(l.split("=", 1) for l in out.value.decode().splitlines())
+
+
+def test_option_defaults_match_the_reference(host):
+    o = _opts(host, "-o", "out.png", "--assets", "a")
+    want = {"ipus": "1", "save-interval": "1", "width": "256", "height": "256", "samples": "512", "samples-per-step": "512",
+            "interactive-samples": "8", "refractive-index": "1.5", "roulette-depth": "3", "stop-prob": "0.3", "aa-noise-scale": "0.3",
+            "fov": "90", "exposure": "0", "gamma": "2.2", "env-map-rotation": "0", "seed": "1", "aa-noise-type": "normal",
+            "max-path-length": "10", "max-nif-batch-size": "44160", "ui-port": "0", "log-level": "info", "enable-load-balancing": "0"}
+    for k, v in want.items():
+        assert o[k] == v, k
+    assert o["outfile"] == "out.png" and o["assets"] == "a"
+
+
+def test_option_forms_and_errors(host):
+    o = _opts(host, "-w", "1104", "-h1000", "--samples=100000", "--samples-per-step", "300", "-o", "x.png", "--assets=/m",
+              "--ipus", "8", "--enable-load-balancing", "-a", "0.5", "-n", "1.33", "--env-map-rotation", "-45")
+    assert (o["width"], o["height"], o["samples"], o["samples-per-step"], o["ipus"]) == ("1104", "1000", "100000", "300", "8")
+    assert o["enable-load-balancing"] == "1" and o["aa-noise-scale"] == "0.5" and o["refractive-index"] == "1.33"
+    assert o["env-map-rotation"] == "-45"
+    with pytest.raises(RuntimeError, match="required but missing"):
+        _opts(host, "-o", "x.png")
+    with pytest.raises(RuntimeError, match="unrecognised option"):
+        _opts(host, "-o", "x.png", "--assets", "a", "--bogus")
+    with pytest.raises(RuntimeError, match="is missing"):
+        _opts(host, "--assets", "a", "-o")
+    with pytest.raises(RuntimeError, match="both save-exe and load-exe"):
+        _opts(host, "-o", "x", "--assets", "a", "--save-exe", "p", "--load-exe", "q")
+    with pytest.raises(RuntimeError, match="Show help"):
+        _opts(host, "--help")
+
+
+def test_round_samples_per_pixel(host):
+    assert host.b200host_round_spp(100000, 300) == 100200        # BASELINE config C2: 334 steps
+    assert host.b200host_round_spp(512, 512) == 512
+    assert host.b200host_round_spp(1, 300) == 300
+
+
+REC = np.dtype([("u", "<u2"), ("v", "<u2"), ("r", "<f4"), ("g", "<f4"), ("b", "<f4"), ("sampleCount", "<u2"), ("pathLength", "<u2")])
+
+
+@pytest.mark.parametrize("w,h,gpus,tile", [(1104, 1000, 1, 16), (1104, 1000, 8, 16), (320, 240, 3, 16), (33, 17, 4, 8), (5, 3, 8, 16), (1, 1, 2, 16)])
+def test_tracing_jobs_cover_every_pixel_once(host, w, h, gpus, tile):
+    per = host.b200host_create_jobs(w, h, gpus, tile, None, 0)
+    assert per > 0
+    items = np.zeros(per * gpus, dtype=REC)
+    assert host.b200host_create_jobs(w, h, gpus, tile, items.ctypes.data_as(C.c_void_p), C.c_size_t(len(items))) == per
+    valid = items[(items["u"] < w) & (items["v"] < h)]
+    pad = items[(items["u"] >= w) | (items["v"] >= h)]
+    assert len(valid) == w * h
+    assert len(np.unique(valid["v"].astype(np.int64) * w + valid["u"])) == w * h
+    assert np.all(pad["u"] == 65535) and np.all(pad["v"] == 65535)          # LoadBalancer.cpp:66-71
+    if w * h >= gpus * tile * tile * 8:
+        counts = [np.sum(items[g * per:(g + 1) * per]["u"] < w) for g in range(gpus)]
+        assert max(counts) - min(counts) <= tile * tile * 2 + tile * max(w, h) // tile
+
+
+def test_load_balancer_deals_cheap_with_expensive(host):
+    rng = np.random.default_rng(3)
+    jobs, per = 4, 250
+    items = np.zeros(jobs * per, dtype=REC)
+    items["u"] = np.arange(len(items)) % 50
+    items["v"] = np.arange(len(items)) // 50
+    items["pathLength"] = rng.integers(1, 2000, len(items))
+    items["r"] = 1.0
+    before = items.copy()
+    rays = host.b200host_balance(items.ctypes.data_as(C.c_void_p), C.c_size_t(per), C.c_size_t(jobs), 1)
+    assert rays == int(before["pathLength"].astype(np.int64).sum())
+    # same multiset of work items, now dealt so that every job's cost is close to the mean
+    key = lambda a: np.sort(a["v"].astype(np.int64) * 1000 + a["u"])
+    assert np.array_equal(key(items), key(before))
+    cost = items["pathLength"].astype(np.int64).reshape(jobs, per).sum(1)
+    naive = before["pathLength"].astype(np.int64).reshape(jobs, per).sum(1)
+    assert cost.max() - cost.min() <= 2000 * 2
+    assert cost.max() - cost.min() <= max(1, naive.max() - naive.min())
+
+
+def _film(host, items, w, h, step, exposure, gamma, name=b""):
+    hdr = np.zeros((h, w, 3), np.float32)
+    ldr = np.zeros((h, w, 3), np.uint8)
+    rc = host.b200host_film_accumulate_save(items.ctypes.data_as(C.c_void_p), C.c_size_t(len(items)), w, h, step, C.c_float(exposure),
+                                            C.c_float(gamma), name, hdr.ctypes.data_as(C.c_void_p), ldr.ctypes.data_as(C.c_void_p))
+    assert rc == 0, host.b200host_last_error()
+    return hdr, ldr
+
+
+def test_film_accumulate_and_tonemap_follow_accumulated_image(host, tmp_path):
+    import cv2
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    rng = np.random.default_rng(5)
+    w, h, spp, step = 37, 21, 7, 3
+    items = np.zeros(w * h + 11, dtype=REC)
+    items["u"][:w * h] = np.arange(w * h) % w
+    items["v"][:w * h] = np.arange(w * h) // w
+    items["u"][w * h:] = 65535
+    items["v"][w * h:] = 65535
+    for k in "rgb":
+        items[k] = rng.gamma(1.5, 2.0, len(items)).astype(np.float32) * spp
+    items["sampleCount"] = spp
+    out = str(tmp_path / "img.png")
+    hdr, ldr = _film(host, items, w, h, step, 0.5, 2.2, out.encode())
+    # AccumulatedImage.cpp:59-74: hdr(v,u) += (b,g,r) / sampleCount, once per step
+    want = np.zeros((h, w, 3), np.float32)
+    v = items[:w * h]
+    for _ in range(step):
+        want[v["v"], v["u"], 0] += v["b"] / np.float32(spp)
+        want[v["v"], v["u"], 1] += v["g"] / np.float32(spp)
+        want[v["v"], v["u"], 2] += v["r"] / np.float32(spp)
+    np.testing.assert_allclose(hdr, want, rtol=1e-6)
+    # :23-46 with OpenCV's own arithmetic: pow, then convertTo(CV_8UC3, 255)
+    scaled = hdr * np.float32(1.0 / step)
+    ref_ldr = cv2.convertScaleAbs(np.power(scaled * np.float32(2.0 ** 0.5), np.float32(1 / 2.2)), alpha=255.0)
+    assert np.abs(ldr.astype(int) - ref_ldr.astype(int)).max() <= 1
+    assert np.mean(ldr == ref_ldr) > 0.99
+    # the files: OpenCV reads back what AccumulatedImage::saveImages would have written with cv::imwrite
+    png = cv2.imread(out, cv2.IMREAD_UNCHANGED)
+    assert png.shape == (h, w, 3) and np.array_equal(png, ldr)
+    exr = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED)
+    assert exr.dtype == np.float32 and exr.shape == (h, w, 3)
+    np.testing.assert_array_equal(exr, scaled)
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (16, 16), (17, 33), (640, 37)])
+def test_png_exr_round_trip_and_interop(host, tmp_path, w, h):
+    import cv2
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    rng = np.random.default_rng(w * 1000 + h)
+    img8 = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    imgf = (rng.standard_normal((h, w, 3)) * 10).astype(np.float32)
+    imgf[0, 0] = [0.0, 1e-30, 6.5e4]
+    p, e = str(tmp_path / "a.png").encode(), str(tmp_path / "a.exr").encode()
+    assert host.b200host_write_png(p, img8.ctypes.data_as(C.c_void_p), w, h) == 0
+    assert host.b200host_write_exr(e, imgf.ctypes.data_as(C.c_void_p), w, h) == 0
+    assert np.array_equal(cv2.imread(p.decode(), cv2.IMREAD_UNCHANGED).reshape(h, w, 3), img8)
+    assert np.array_equal(cv2.imread(e.decode(), cv2.IMREAD_UNCHANGED).reshape(h, w, 3), imgf)
+    # our readers on our files
+    ww, hh = C.c_uint32(), C.c_uint32()
+    back8 = np.zeros_like(img8)
+    assert host.b200host_read_png(p, back8.ctypes.data_as(C.c_void_p), C.c_size_t(back8.size), C.byref(ww), C.byref(hh)) == 0
+    assert (ww.value, hh.value) == (w, h) and np.array_equal(back8, img8)
+    backf = np.zeros_like(imgf)
+    assert host.b200host_read_exr(e, backf.ctypes.data_as(C.c_void_p), C.c_size_t(backf.size), C.byref(ww), C.byref(hh)) == 0
+    assert (ww.value, hh.value) == (w, h) and np.array_equal(backf, imgf)
+    # our readers on OpenCV's files (what the reference itself writes)
+    p2, e2 = str(tmp_path / "b.png"), str(tmp_path / "b.exr")
+    cv2.imwrite(p2, img8)
+    cv2.imwrite(e2, imgf, [cv2.IMWRITE_EXR_TYPE, cv2.IMWRITE_EXR_TYPE_FLOAT])
+    assert host.b200host_read_png(p2.encode(), back8.ctypes.data_as(C.c_void_p), C.c_size_t(back8.size), C.byref(ww), C.byref(hh)) == 0
+    assert np.array_equal(back8, img8)
+    rc = host.b200host_read_exr(e2.encode(), backf.ctypes.data_as(C.c_void_p), C.c_size_t(backf.size), C.byref(ww), C.byref(hh))
+    if rc == 0:          # OpenCV may pick a compression this reader does not implement (PIZ); NONE/ZIP(S) must agree
+        assert np.array_equal(backf, imgf)
+    else:
+        assert b"compression" in host.b200host_last_error()
+
+
+def _assets(tmp_path, model=None, meta=METADATA, h5=None, **h5kw):
+    d = tmp_path / "assets.extra"
+    d.mkdir(exist_ok=True)
+    (d / "nif_metadata.txt").write_text(json.dumps(meta, indent=2))
+    if model is not None and h5 is None:
+        from ipu_path_trace_b200.nif import write_nif_bin
+        write_nif_bin(str(d / "nif.bin"), model)
+    if h5:
+        from h5_writer import write_keras_nif
+        write_keras_nif(str(d / "converted.hdf5"), model, **h5kw)
+    return str(d)
+
+
+def _load(host, path, synthetic=0):
+    out = C.create_string_buffer(4096)
+    k0 = np.zeros(48 * 320, np.uint16)
+    rc = host.b200host_load_assets(path.encode(), synthetic, out, len(out), k0.ctypes.data_as(C.c_void_p), C.c_size_t(k0.size))
+    if rc:
+        raise RuntimeError(host.b200host_last_error().decode())
+    s = out.value.decode()
+    shapes = s.split(";shapes=")[1].split(";")[0]
+    fields = dict(kv.split("=", 1) for kv in s.replace(";shapes=" + shapes, "").split(";"))
+    return fields, shapes, k0
+
+
+def test_metadata_and_nif_bin_loader(host, tmp_path):
+    from ipu_path_trace_b200.nif import synthetic_model
+    m = synthetic_model()
+    f, shapes, k0 = _load(host, _assets(tmp_path, m))
+    assert f["layers"] == "7" and f["E"] == "12" and f["hidden"] == "320" and f["log"] == "1"
+    assert int(f["flops"]) == m.flops_per_eval() == 1089283
+    assert shapes == "48x320rbh|320x320rbh|320x320rbh|368x320rbh|320x320rbh|320x320rbh|320x3nbh|"
+    assert np.array_equal(k0, m.layers[0]["kernel"].view(np.uint16).reshape(-1))
+    # NifMetaData.cpp:48-53: eps folded into the mean when log tone mapping
+    mean = [float(x) for x in f["mean"].split(",")]
+    for got, raw in zip(mean, METADATA["encode_params"]["mean"]):
+        assert np.float32(got) == np.float32(np.float32(raw) - np.float32(1e-8))
+    assert np.float32(float(f["max"])) == np.float32(3.4299468994140625)
+
+
+def test_asset_errors(host, tmp_path):
+    with pytest.raises(RuntimeError, match="Could not open file"):
+        _load(host, str(tmp_path / "missing"))
+    p = _assets(tmp_path)
+    with pytest.raises(RuntimeError, match="No weights"):
+        _load(host, p)
+    f, shapes, _ = _load(host, p, synthetic=1)
+    assert f["source"].startswith("synthetic") and shapes.count("|") == 7
+    bad = dict(METADATA); del bad["encode_params"]
+    (tmp_path / "b").mkdir()
+    with pytest.raises(RuntimeError, match="Error reading property"):
+        _load(host, _assets(tmp_path / "b", meta=bad), synthetic=1)
+    (tmp_path / "c" ).mkdir()
+    d = _assets(tmp_path / "c")
+    open(os.path.join(d, "nif_metadata.txt"), "w").write("{ not json")
+    with pytest.raises(RuntimeError, match="JSON parse error"):
+        _load(host, d, synthetic=1)
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(vlen_attrs=True), dict(dtype=np.float32), dict(chunked=True), dict(chunked=True, dtype=np.float32, vlen_attrs=True)])
+def test_keras_hdf5_weights_load_like_hdf5model(host, tmp_path, kw):
+    """converted.hdf5 laid out as Keras/h5py write it (tests/h5_writer.py, from the format specification)
+    is read by the host's HDF5 subset exactly as Hdf5Model.cpp:62-133 would hand it over."""
+    from ipu_path_trace_b200.nif import synthetic_model
+    m = synthetic_model(seed=7)
+    path = _assets(tmp_path, m, h5=True, **kw)
+    f, shapes, k0 = _load(host, path)
+    half = kw.get("dtype", np.float16) == np.float16
+    t = "h" if half else "f"
+    assert shapes == f"48x320rb{t}|320x320rb{t}|320x320rb{t}|368x320rb{t}|320x320rb{t}|320x320rb{t}|320x3nb{t}|"
+    assert f["source"].endswith("converted.hdf5") and int(f["flops"]) == 1089283
+    if half:
+        assert np.array_equal(k0, m.layers[0]["kernel"].view(np.uint16).reshape(-1))
+    # dataset / attribute / listing entry points
+    h5 = os.path.join(path, "converted.hdf5").encode()
+    shape = (C.c_size_t * 4)()
+    rank, es = C.c_int(4), C.c_size_t()
+    buf = np.zeros(368 * 320 * 4, np.uint8)
+    assert host.b200host_h5_dataset(h5, b"/model_weights/dense_3/dense_3/kernel:0", buf.ctypes.data_as(C.c_void_p), C.c_size_t(buf.size),
+                                    shape, C.byref(rank), C.byref(es)) == 0, host.b200host_last_error()
+    assert rank.value == 2 and (shape[0], shape[1]) == (368, 320) and es.value == (2 if half else 4)
+    want = np.asarray(m.layers[3]["kernel"], dtype=np.float16 if half else np.float32)
+    assert np.array_equal(buf[:want.nbytes].view(want.dtype).reshape(368, 320), want)
+    out = C.create_string_buffer(1 << 15)
+    assert host.b200host_h5_attribute(h5, b"/", b"keras_version", out, len(out)) == 0 and out.value == b"2.6.0"
+    assert host.b200host_h5_attribute(h5, b"/", b"backend", out, len(out)) == 0 and out.value == b"tensorflow"
+    assert host.b200host_h5_attribute(h5, b"/", b"model_config", out, len(out)) == 0
+    cfg = json.loads(out.value.decode())
+    assert cfg["class_name"] == "Functional" and sum(l["class_name"] == "Dense" for l in cfg["config"]["layers"]) == 7
+    assert host.b200host_h5_list(h5, b"/model_weights", out, len(out)) == 0
+    names = out.value.decode().split()
+    assert names == sorted(names) and len(names) == 9 and "dense_6" in names
+    assert host.b200host_h5_dataset(h5, b"/model_weights/nope", buf.ctypes.data_as(C.c_void_p), C.c_size_t(buf.size), shape, C.byref(rank), C.byref(es)) != 0
+    assert b"doesn't exist" in host.b200host_last_error()
+
+
+def test_hdf5_reader_rejects_garbage(host, tmp_path):
+    p = tmp_path / "x.hdf5"
+    p.write_bytes(b"not an hdf5 file" * 10)
+    out = C.create_string_buffer(64)
+    assert host.b200host_h5_attribute(str(p).encode(), b"/", b"a", out, len(out)) != 0
+    assert b"not an HDF5 file" in host.b200host_last_error()
+    from ipu_path_trace_b200.nif import synthetic_model
+    from h5_writer import write_keras_nif
+    good = tmp_path / "g.hdf5"
+    write_keras_nif(str(good), synthetic_model(hidden=64, hidden_layers=2, concat_at=1, embedding_dimension=4))
+    data = good.read_bytes()
+    (tmp_path / "t.hdf5").write_bytes(data[:len(data) // 3])       # truncated file: an error, never a crash
+    rc = host.b200host_h5_attribute(str(tmp_path / "t.hdf5").encode(), b"/", b"model_config", out, len(out))
+    assert rc != 0 and b"HDF5" in host.b200host_last_error()
+
+
+def test_cli_binary_fails_loudly_without_gpu(tmp_path):
+    """The product has no CPU path: without a CUDA device the CLI exits non-zero with the library's message."""
+    subprocess.run(["make", "-C", HOST, "b200_path_trace"], check=True, capture_output=True)
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    d = _assets(tmp_path)
+    r = subprocess.run([os.path.join(HOST, "b200_path_trace"), "-o", str(tmp_path / "o.png"), "--assets", d, "--synthetic-weights", "-w", "32", "-h", "32"],
+                       capture_output=True, text=True)
+    assert r.returncode != 0
+    assert "no CUDA device" in r.stderr and "no CPU path" in r.stderr
+    assert not (tmp_path / "o.png").exists()
