@@ -226,8 +226,9 @@ RenderSummary PathTracerApp::execute() {
       logging::debug("GPU {}: path-trace {} ms, NIF {} ms, total {} ms", gpus[g]->device, ctr.trace_ms, ctr.nif_ms, ctr.total_ms);
     }
 
-    // Wait for completion of previous async task before starting the next (:702-706):
-    hostProcessing.waitForCompletion();
+    // Wait for completion of previous async task before starting the next (:702-706). With the device film
+    // the host thread only ever holds a gathered copy, so the wait moves to the next gather.
+    if (recordStream) hostProcessing.waitForCompletion();
 
     const bool saveNow = (step % saveInterval == 0) || step == steps;
     if (recordStream) {
@@ -248,6 +249,7 @@ RenderSummary PathTracerApp::execute() {
       totalRays = stepRays;
       if (saveNow) {
         // one gather per save interval; encoding and writing the files overlaps the next steps
+        hostProcessing.waitForCompletion();
         gatherDeviceFilm(film);
         hostProcessing.run([&, step]() {
           film.saveImages(fileName, step, exposure, gamma);

@@ -214,10 +214,13 @@ void writeExr(const std::string& path, const float* bgr, uint32_t width, uint32_
   out.resize(out.size() + (size_t)blocks * 8, 0);
 
   const size_t lineBytes = (size_t)width * 3 * sizeof(float);
-  std::vector<uint8_t> raw;
-  for (uint32_t b = 0; b < blocks; ++b) {
+  // blocks are independent: pre-condition and deflate them in parallel, then lay them out in order
+  std::vector<std::vector<uint8_t>> packed(blocks);
+#pragma omp parallel for schedule(dynamic)
+  for (int64_t bi = 0; bi < (int64_t)blocks; ++bi) {
+    const uint32_t b = (uint32_t)bi;
     const uint32_t y0 = b * kZipLines, y1 = std::min(height, y0 + kZipLines);
-    raw.resize(lineBytes * (y1 - y0));
+    std::vector<uint8_t> raw(lineBytes * (y1 - y0));
     float* dst = reinterpret_cast<float*>(raw.data());
     for (uint32_t y = y0; y < y1; ++y)
       for (int c = 0; c < 3; ++c) {                           // planar per line: all B, all G, all R
@@ -225,14 +228,15 @@ void writeExr(const std::string& path, const float* bgr, uint32_t width, uint32_
         for (uint32_t x = 0; x < width; ++x) *dst++ = src[(size_t)x * 3];
       }
     const std::vector<uint8_t> pre = zipPrecondition(raw.data(), raw.size());
-    const std::vector<uint8_t> z = deflateAll(pre.data(), pre.size(), 4);
-    const bool useZ = z.size() < raw.size();
+    std::vector<uint8_t> z = deflateAll(pre.data(), pre.size(), 4);
+    packed[b] = z.size() < raw.size() ? std::move(z) : std::move(raw);
+  }
+  for (uint32_t b = 0; b < blocks; ++b) {
     const uint64_t off = out.size();
     std::memcpy(out.data() + tablePos + (size_t)b * 8, &off, 8);
-    putLe<int32_t>(out, (int32_t)y0);
-    putLe<int32_t>(out, (int32_t)(useZ ? z.size() : raw.size()));
-    if (useZ) out.insert(out.end(), z.begin(), z.end());
-    else out.insert(out.end(), raw.begin(), raw.end());
+    putLe<int32_t>(out, (int32_t)(b * kZipLines));
+    putLe<int32_t>(out, (int32_t)packed[b].size());
+    out.insert(out.end(), packed[b].begin(), packed[b].end());
   }
   writeFile(path, out);
 }

@@ -153,13 +153,16 @@ def load_assets(assets_dir: str, allow_synthetic: bool = False) -> tuple[NifMode
     """--assets <dir>: reads assets.extra/nif_metadata.txt (PathTracerApp.cpp:106-123) and the weights:
     assets.extra/nif.bin if present. The Keras HDF5 (converted.hdf5) needs h5py, absent here.
     Returns (model, metadata, source) where source says where the weights came from."""
-    meta_path = os.path.join(assets_dir, "assets.extra", "nif_metadata.txt")
+    # the reference's --assets is the assets.extra directory itself (PathTracerApp.cpp:106-110); the saved
+    # Keras model directory that contains it is accepted too
+    if not os.path.exists(os.path.join(assets_dir, "nif_metadata.txt")) and os.path.isdir(os.path.join(assets_dir, "assets.extra")):
+        assets_dir = os.path.join(assets_dir, "assets.extra")
+    meta_path = os.path.join(assets_dir, "nif_metadata.txt")
     meta = NifMetaData.load(meta_path)
-    bin_path = os.path.join(assets_dir, "assets.extra", "nif.bin")
+    bin_path = os.path.join(assets_dir, "nif.bin")
     if os.path.exists(bin_path):
         m = read_nif_bin(bin_path)
         return NifModel(meta.embedding_dimension, meta.max, meta.mean, meta.log_tone_map, m.layers), meta, bin_path
     if allow_synthetic:
         return synthetic_model(meta), meta, "synthetic(seed=42)"
-    raise RuntimeError(f"no weights under {assets_dir}/assets.extra (nif.bin missing; converted.hdf5 needs "
-                       "tools/h5_to_nifbin.py where h5py exists)")
+    raise RuntimeError(f"no weights under {assets_dir} (nif.bin missing; converted.hdf5 is read by the C++ host, host/Hdf5File.cpp)")
