@@ -48,6 +48,17 @@ def measured_peaks():
     return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def nif_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE nif_tc_kernel launch of this very workload
+    (one wavefront of C2), from the committed `ncu --set full` capture (profiles/r1_nif_tc_traffic.json);
+    None when no capture has been committed."""
+    p = os.path.join(ROOT, "profiles", "r1_nif_tc_traffic.json")
+    if not os.path.exists(p):
+        return None
+    d = json.load(open(p))
+    return float(d["dram_bytes_read_per_launch"]) + float(d["dram_bytes_write_per_launch"])
+
+
 class ClockSampler:
     """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -287,7 +298,7 @@ def run_ours(args) -> None:
             "gpu_launches": int(launches),
             "clocks": clk,
             "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
-                         "traffic": None, "kernel": "nif_tc_kernel", "peak_source": peak_src,
+                         "traffic": nif_traffic_bytes(), "kernel": "nif_tc_kernel", "peak_source": peak_src,
                          "whole_step_frac": (flops_per_eval * escaped / world) / (dev_ms * 1e-3) / 1e12 / peak_tf if dev_ms > 0 else 0.0},
         }
         if world == 1 and not args.no_cpu_baseline:
