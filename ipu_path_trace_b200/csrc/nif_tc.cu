@@ -74,6 +74,14 @@ __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
     if (++spins > (1u << 26)) __trap();
   }
 }
+// Non-blocking poll: 1 if the phase with this parity has completed. The result is a plain register, so
+// the poll's latency overlaps whatever is issued before its first use.
+__device__ __forceinline__ uint32_t mbarTest(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+               : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done;
+}
 __device__ __forceinline__ void bulkCopyG2S(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
@@ -345,6 +353,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     const uint32_t ringLo = (((sbase + L.ring) & 0x3FFFFu) >> 4);
     uint32_t stage = 0, phase = 0;
     uint32_t actUse0 = 0, actUse1 = 0;     // completed waits on act_ready[part]
+    uint32_t wLanded = 0;                  // the current chunk's weights were seen landed by the early poll
     uint32_t it = 0;
     long long pFeat = 0, pAcc = 0, pAct = 0, pW = 0, pOutE = 0, pPeer = 0, pIssue = 0; const long long pStart = PROF_T(); (void)pStart;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
@@ -368,7 +377,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           else if (waitAct == 2) { mbarWait<CG>(bar(BAR_ACT_READY + 1), actUse1 & 1u); actUse1 += 1; }
           PROF_ADD(pAct, t0); }
         { const long long t0 = PROF_T();
-          mbarWait<CG>(bar(BAR_W_FULL + stage), phase);
+          if (!wLanded) mbarWait<CG>(bar(BAR_W_FULL + stage), phase);       // usually polled ahead, see below
           PROF_ADD(pW, t0);
           const long long t1 = PROF_T();
           if (CG == 2) mbarWait<CG>(bar(BAR_PEER_W_FULL + stage), phase);
@@ -383,11 +392,17 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         const uint32_t idesc = umInstr<CG>(n8);
         const uint32_t bStep = bRows * 2u;                                            // rows * 32 bytes per K-step
         uint32_t acc = (flags & kChFirst) ? 0u : 1u;
+        // The next chunk's weights are polled (non-blocking) between two MMAs of this chunk: the producer is
+        // normally a full ring ahead, so the blocking wait - a dependent poll in the gap between chunks, where
+        // the shallow tensor queue runs dry - is skipped almost always.
+        const uint32_t nStage = (stage + 1 == (uint32_t)kStages) ? 0u : stage + 1u;
+        const uint32_t nPhase = (stage + 1 == (uint32_t)kStages) ? (phase ^ 1u) : phase;
         const long long tIssue = PROF_T();
         // Two separate loops: a predicated-off twin UTCHMMA still occupies a tensor-queue slot.
         if (aFromTmem) {
 #pragma unroll
           for (uint32_t j = 0; j < (uint32_t)KC; ++j) {
+            if (j == 1) wLanded = (CG == 1) ? mbarTest(bar(BAR_W_FULL + nStage), nPhase) : 0u;
             if (j < ksteps) {
               if (leader) tcMmaTs<CG>(dT, aTm, bLo, kDescHi, idesc, acc);
               aTm += 8u; bLo += bStep; acc = 1u;
@@ -396,6 +411,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         } else {
 #pragma unroll
           for (uint32_t j = 0; j < (uint32_t)KC; ++j) {
+            if (j == 1) wLanded = (CG == 1) ? mbarTest(bar(BAR_W_FULL + nStage), nPhase) : 0u;
             if (j < ksteps) {
               if (leader) tcMma<CG>(dT, aLo, bLo, kDescHi, idesc, acc);
               aLo += 256u; bLo += bStep; acc = 1u;
