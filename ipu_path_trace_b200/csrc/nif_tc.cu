@@ -250,7 +250,11 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
   const uint32_t accCol0 = TS ? (uint32_t)NH : 0u;      // TS: columns [0, H/2) hold the activations
   const uint32_t outCol = 3u * (uint32_t)NH;            // output accumulator (16 columns)
   const uint32_t sbase = smemAddr(smem);
-  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  // The warp index is broadcast from lane 0 so that ptxas knows the role branches below are warp-uniform:
+  // only then does it keep the MMA warp's descriptors, barrier addresses and loop state on the uniform
+  // datapath (UTCHMMA needs uniform registers) - 9-12 instructions per tcgen05.mma instead of 18-22 with
+  // per-MMA R2UR / VOTEU marshalling.
+  const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31u;
   static_assert(!(MC && CG == 2), "weight multicast is the single-CTA-MMA alternative to the CTA pair");
   constexpr uint32_t CL = (CG == 2 || MC) ? 2u : 1u;     // CTAs per cluster = tiles per work unit
   const uint32_t rank = (CL == 2) ? clusterCtaRank() : 0u;
