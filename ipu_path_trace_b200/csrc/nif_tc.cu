@@ -30,7 +30,8 @@ namespace b2 {
 constexpr int kTcRows = 128;
 constexpr int kEncodeWarps = 4;
 constexpr int kEpiWarps = 8;
-constexpr int kTcThreads = 32 * (2 + kEncodeWarps + kEpiWarps);
+constexpr int kTcThreads = 32 * (3 + kEncodeWarps + kEpiWarps);
+constexpr int kSecondIssuerWarp = 2 + kEncodeWarps + kEpiWarps;   // single-CTA MMA variants issue from two warps in turn
 constexpr int kFirstEncodeWarp = 2;
 constexpr int kFirstEpiWarp = 2 + kEncodeWarps;
 constexpr uint32_t kTmemCols = 512;
@@ -217,7 +218,8 @@ __host__ __device__ inline TcSmem tcLayout(int H, int featKSteps, int numHidden,
 
 // barrier indices inside the bars block
 enum { BAR_W_FULL = 0, BAR_W_EMPTY = 8, BAR_PEER_W_FULL = 16, BAR_FEAT_FULL = 24, BAR_FEAT_EMPTY = 26,
-       BAR_ACC_FULL = 28, BAR_ACC_EMPTY = 31, BAR_ACT_READY = 34, BAR_OUT_FULL = 36, BAR_OUT_EMPTY = 37, BAR_COUNT = 38 };
+       BAR_ACC_FULL = 28, BAR_ACC_EMPTY = 31, BAR_ACT_READY = 34, BAR_OUT_FULL = 36, BAR_OUT_EMPTY = 37, BAR_COUNT = 38,
+       SLOT_TURN = 40 /* not a barrier: index of the chunk whose MMAs may be issued next */ };
 
 // CG = 1: one CTA per SM, M = 128 MMAs. CG = 2: a cluster of two CTAs (one TPC) runs M = 256 MMAs
 // issued by the rank-0 CTA; each CTA encodes, stores and post-processes its own 128-row tile and
@@ -287,6 +289,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       mbarInit(bar(BAR_ACT_READY + b), CG * kEpiWarps);
     }
     for (int b = 0; b < (int)kSlots; ++b) { mbarInit(bar(BAR_ACC_FULL + b), 1); mbarInit(bar(BAR_ACC_EMPTY + b), CG * kEpiWarps); }
+    *reinterpret_cast<volatile uint32_t*>(smem + L.bars + 8 * SLOT_TURN) = 0u;
     mbarInit(bar(BAR_OUT_FULL), 1);
     mbarInit(bar(BAR_OUT_EMPTY), CG * kEpiWarps / 2);
     fenceBarrierInit();
@@ -348,8 +351,16 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // ================= MMA issuer (converged warp, one elected lane issues) =================
+  } else if (warp == 1 || (CG == 1 && warp == (uint32_t)kSecondIssuerWarp)) {
+    // ================= MMA issuers (converged warps, one elected lane issues) =================
+    // tcgen05.mma issue blocks while the (shallow) tensor queue is full, so whatever the issuing warp does
+    // between the last MMA of a chunk and the first of the next - decode the chunk, poll its barriers, build
+    // descriptors - leaves the tensor pipe idle. With one CTA per MMA group two warps take the chunks in turn:
+    // while one issues, the other has already waited for and prepared the next chunk and only waits for the
+    // "turn" word; the hand-over costs one shared-memory round trip.
+    constexpr bool kDual = (CG == 1);
+    const uint32_t me = (warp == 1) ? 0u : 1u;
+    const uint32_t turnAddr = sbase + L.bars + 8u * SLOT_TURN;
     const bool leader = electOne();
     // Descriptor start addresses are 14-bit fields of (address & 0x3FFFF) >> 4: in a cluster launch the
     // shared-window address of an odd-ranked CTA carries the rank above bit 18 and must be masked off.
@@ -367,6 +378,13 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       for (int c = 0; c < numChunks; ++c) {
         const NifTcChunk& ch = m.chunks[c];
         const uint32_t ksteps = ch.ksteps, n8 = ch.n8, flags = ch.flags, waitAct = ch.waitAct;
+        const uint32_t g = it * (uint32_t)numChunks + (uint32_t)c;        // running chunk index = turn number
+        if (kDual && (g & 1u) != me) {
+          // the other warp's chunk: only keep the counters in step
+          if (waitAct == 1) actUse0 += 1; else if (waitAct == 2) actUse1 += 1;
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          continue;
+        }
         const bool isOut = (flags & kChOut) != 0;
         // the two half-jobs of a layer accumulate concurrently (K order above): the accumulator slot
         // and how often the slot was used before in this tile come precomputed with the chunk
@@ -381,7 +399,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           else if (waitAct == 2) { mbarWait<CG>(bar(BAR_ACT_READY + 1), actUse1 & 1u); actUse1 += 1; }
           PROF_ADD(pAct, t0); }
         { const long long t0 = PROF_T();
-          if (!wLanded) mbarWait<CG>(bar(BAR_W_FULL + stage), phase);       // usually polled ahead, see below
+          if (kDual || !wLanded) mbarWait<CG>(bar(BAR_W_FULL + stage), phase);       // single issuer: usually polled ahead, see below
           PROF_ADD(pW, t0);
           const long long t1 = PROF_T();
           if (CG == 2) mbarWait<CG>(bar(BAR_PEER_W_FULL + stage), phase);
@@ -401,12 +419,24 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         // the shallow tensor queue runs dry - is skipped almost always.
         const uint32_t nStage = (stage + 1 == (uint32_t)kStages) ? 0u : stage + 1u;
         const uint32_t nPhase = (stage + 1 == (uint32_t)kStages) ? (phase ^ 1u) : phase;
+        if (kDual) {
+          // everything is ready: wait until the other warp has issued the previous chunk
+          const long long t0 = PROF_T();
+          uint32_t cur, spins = 0;
+          while (true) {
+            asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(cur) : "r"(turnAddr) : "memory");
+            if (cur == g) break;
+            if (++spins > (1u << 28)) __trap();        // a protocol bug must fault, not hang the GPU
+          }
+          tcFenceAfter();
+          PROF_ADD(pPeer, t0);
+        }
         const long long tIssue = PROF_T();
         // Two separate loops: a predicated-off twin UTCHMMA still occupies a tensor-queue slot.
         if (aFromTmem) {
 #pragma unroll
           for (uint32_t j = 0; j < (uint32_t)KC; ++j) {
-            if (j == 1) wLanded = (CG == 1) ? mbarTest(bar(BAR_W_FULL + nStage), nPhase) : 0u;
+            if (j == 1 && !kDual) wLanded = mbarTest(bar(BAR_W_FULL + nStage), nPhase);
             if (j < ksteps) {
               if (leader) tcMmaTs<CG>(dT, aTm, bLo, kDescHi, idesc, acc);
               aTm += 8u; bLo += bStep; acc = 1u;
@@ -415,7 +445,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
         } else {
 #pragma unroll
           for (uint32_t j = 0; j < (uint32_t)KC; ++j) {
-            if (j == 1) wLanded = (CG == 1) ? mbarTest(bar(BAR_W_FULL + nStage), nPhase) : 0u;
+            if (j == 1 && !kDual) wLanded = mbarTest(bar(BAR_W_FULL + nStage), nPhase);
             if (j < ksteps) {
               if (leader) tcMma<CG>(dT, aLo, bLo, kDescHi, idesc, acc);
               aLo += 256u; bLo += bStep; acc = 1u;
@@ -427,12 +457,16 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           if (flags & kChLast) tcCommit<CG>(bar(isOut ? BAR_OUT_FULL : BAR_ACC_FULL + buf));
           if (flags & kChLastFeatUse) tcCommit<CG>(bar(BAR_FEAT_EMPTY + fb));
         }
+        if (kDual) {
+          tcFenceBefore();
+          if (leader) asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(turnAddr), "r"(g + 1u) : "memory");
+        }
         PROF_ADD(pIssue, tIssue);
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
 #ifdef B200PT_PROFILE
-    if (lane == 0) { unsigned long long* p = g_tcProf + blockIdx.x * 16; p[0] = clock64() - pStart; p[1] = pFeat; p[2] = pAcc; p[3] = pAct; p[4] = pW; p[5] = pOutE; p[6] = it; p[7] = pPeer; p[15] = pIssue; }
+    if (lane == 0 && me == 0) { unsigned long long* p = g_tcProf + blockIdx.x * 16; p[0] = clock64() - pStart; p[1] = pFeat; p[2] = pAcc; p[3] = pAct; p[4] = pW; p[5] = pOutE; p[6] = it; p[7] = pPeer; p[15] = pIssue; }
 #endif
     __syncwarp();
   } else if (warp < kFirstEpiWarp) {
@@ -465,7 +499,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       __syncwarp();
       if (lane == 0) arriveIssuer(BAR_FEAT_FULL + fb);
     }
-  } else {
+  } else if (warp < (uint32_t)kSecondIssuerWarp) {
     // ================= epilogue =================
     const uint32_t ew = warp - kFirstEpiWarp;
     const uint32_t quad = warp & 3u;                      // TMEM lane quadrant this warp may read
