@@ -107,6 +107,7 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
 
   const size_t cap = cfg->max_worklist;
   uint32_t spl = cfg->samples_per_launch;
+  if (spl == 0) if (const char* e = getenv("B200PT_SPL")) spl = (uint32_t)std::max(0, std::atoi(e));    // A/B runs only
   if (spl == 0) {
     // automatic: enough escaped rays per wavefront to fill every SM with >= 64 tiles of 128 rows,
     // bounded so the queue stays below ~1 GiB.

@@ -508,7 +508,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     const uint32_t colsMine = (uint32_t)NH / 2u;          // multiple of 16, <= 80
     const uint32_t groups = colsMine / 16u;               // <= 5
     const uint32_t laneBase = tmemBase + ((quad * 32u) << 16);
-    const __half2 zero2 = __float2half2_rn(0.f);
+    const __half2 one2 = __float2half2_rn(1.f);
     uint32_t it = 0;
     long long eWait = 0, eWork = 0, eOutWait = 0, eOutWork = 0; const long long eStart = PROF_T(); (void)eStart;
     for (uint32_t unit = unit0; unit < numUnits; unit += unitStride, ++it) {
@@ -539,8 +539,9 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
                 __half2 hv = __floats2half2_rn(__uint_as_float(v[g & 1][2 * q]), __uint_as_float(v[g & 1][2 * q + 1]));
-                hv = __hadd2(hv, *reinterpret_cast<const __half2*>(&bw[q]));
-                if (relu) hv = __hmax2(hv, zero2);
+                // x * 1 + bias is one rounding, like the add; the relu variant clamps in the same instruction
+                const __half2 bq = *reinterpret_cast<const __half2*>(&bw[q]);
+                hv = relu ? __hfma2_relu(hv, one2, bq) : __hadd2(hv, bq);
                 packed[q] = *reinterpret_cast<uint32_t*>(&hv);
               }
               if (TS) {
