@@ -160,7 +160,7 @@ void b200pt_destroy(b200pt_ctx* c) {
   c->qUv.release(); c->qThrSlot.release(); c->qCount.release(); c->stats.release();
   c->scene.release(); c->film.release(); c->filmOut.release(); c->film8.release();
   for (auto& s : c->scratch) s.release();
-  c->simtParams.release(); c->tcStream.release(); c->tcBias.release();
+  c->simtParams.release(); c->tcStream.release(); c->tcBias.release(); c->tcFeatTable.release();
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }

@@ -211,6 +211,24 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
     for (int l = 0; l < numHidden; ++l) for (int i = 0; i < H; ++i) bias[(size_t)l * H + i] = ls[l].b[i];
     CU(c, c->tcBias.alloc(bias.size()));
     CU(c, cudaMemcpy(c->tcBias.p, bias.data(), bias.size() * 2, cudaMemcpyHostToDevice));
+    // Feature table. The encoder's argument of octave i is binary16(p * 2^i) (NifModel.cpp:211-213) and rounding to
+    // binary16 commutes with the power of two, so all 4E features of a coordinate are a function of the 16 bits of
+    // binary16(p): one row of E (sin, cos) pairs per bit pattern, evaluated here with the host libm exactly as the
+    // CPU twin does (NifModel.cpp:404-432). 65536 x E x 4 bytes (3 MB for E = 12), L2 resident.
+    {
+      std::vector<uint32_t> table((size_t)65536 * E);
+      for (uint32_t bits = 0; bits < 65536u; ++bits) {
+        const float x0 = hostHalfToFloat((uint16_t)bits);
+        float coeff = 1.f;
+        for (int i = 0; i < E; ++i, coeff *= 2.f) {
+          const float x = hostRoundHalf(x0 * coeff);
+          const uint16_t sb = hostFloatToHalf(sinf(x)), cb = hostFloatToHalf(cosf(x));
+          table[(size_t)bits * E + i] = (uint32_t)sb | ((uint32_t)cb << 16);
+        }
+      }
+      CU(c, c->tcFeatTable.alloc(table.size()));
+      CU(c, cudaMemcpy(c->tcFeatTable.p, table.data(), table.size() * 4, cudaMemcpyHostToDevice));
+    }
     // Kernel variant. Default (mc10): activations in tensor memory, 10 K-steps per chunk, weight chunks
     // multicast between the two CTAs of a cluster. B200PT_NIF_MODE = ss1 | ss2 | ts5 | ts10 | tp5 | tp10 |
     // mc5 | mc10 selects another one (A/B measurements and the parity tests of each variant).
@@ -233,7 +251,7 @@ int b200pt_upload_nif(b200pt_ctx* c, const b200pt_nif_desc* nif) {
     else {
       CU(c, c->tcStream.alloc(stream.size()));
       CU(c, cudaMemcpy(c->tcStream.p, stream.data(), stream.size(), cudaMemcpyHostToDevice));
-      tm.wStream = c->tcStream.p; tm.bias = c->tcBias.p;
+      tm.wStream = c->tcStream.p; tm.bias = c->tcBias.p; tm.featTable = c->tcFeatTable.p;
       if (nifTcSmemBytes(tm) > 227 * 1024 || nifTcStages(tm) < 2) { c->tcOk = false; c->tcWhyNot = "tcgen05 kernel shared memory exceeds 227 KB"; }
       else {
         CU(c, prepareNifTc(tm));

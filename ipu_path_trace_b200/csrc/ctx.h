@@ -89,6 +89,7 @@ struct b200pt_ctx {
   DevBuf<uint8_t> tcStream;
   int tcMaxPairs = 0;
   DevBuf<__half> tcBias;
+  DevBuf<uint32_t> tcFeatTable;
 
   b200pt_counters counters{};
   bool pending = false;      // a path_trace is enqueued and not yet folded into counters

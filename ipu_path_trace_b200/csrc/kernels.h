@@ -75,6 +75,7 @@ struct NifTcModel {
                                // weight chunks multicast between the two CTAs of a cluster
   const uint8_t* wStream;      // packed chunks (device)
   const __half* bias;          // [numHidden][H] (device; zeros where a layer has no bias)
+  const uint32_t* featTable;   // [65536][E] (sin, cos) binary16 pairs of all E octaves for every binary16 value of p = (uv-1)*2
   float bOut[4];
   int finalHasBias;
   float maxv, mean[3];

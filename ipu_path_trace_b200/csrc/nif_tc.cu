@@ -482,7 +482,25 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
       __half f[kMaxFeatures];
 #pragma unroll
       for (int k = 0; k < kMaxFeatures; ++k) f[k] = __float2half_rn(0.f);
-      nifEncode(uv.x, uv.y, E, [&](int k, __half v) { f[k] = v; });
+      // All octaves of one coordinate come from one table row (see b200pt_upload_nif). Values of p whose
+      // binary16 form is subnormal or not finite take the arithmetic path (rounding no longer commutes there).
+      auto encodeCoord = [&](float t, int base) {
+        const float p = (t - 1.f) * 2.f;
+        const float ap = fabsf(p);
+        if (ap >= 6.103515625e-05f && ap < 65520.f) {
+          const uint32_t* row = m.featTable + (size_t)__half_as_ushort(__float2half_rn(p)) * (uint32_t)E;
+          for (int i = 0; i < E; ++i) {
+            const uint32_t sc = __ldg(row + i);
+            f[base + i] = __ushort_as_half((unsigned short)(sc & 0xffffu));
+            f[2 * E + base + i] = __ushort_as_half((unsigned short)(sc >> 16));
+          }
+        } else {
+          float coeff = 1.f;
+          for (int i = 0; i < E; ++i, coeff *= 2.f) nifFeaturePair(p, coeff, f[base + i], f[2 * E + base + i]);
+        }
+      };
+      encodeCoord(uv.x, 0);
+      encodeCoord(uv.y, E);
       // wait until the MMAs of the unit that last used this buffer are done with it
       mbarWait<CG>(bar(BAR_FEAT_EMPTY + fb), fpar ^ 1u);
       unsigned char* fbuf = smem + L.feat[fb];
