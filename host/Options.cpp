@@ -52,6 +52,7 @@ Options::Options() {
       "(setup / path_trace / read_results per step). Default: device film, one gather per save interval.");
   add("synthetic-weights", 0, true, false, "", "Use seeded synthetic NIF weights in the topology of nif_metadata.txt when the assets hold no weights.");
   add("devices", 0, false, false, "", "Comma separated CUDA device ordinals (default 0..ipus-1).");
+  add("ui-accept-timeout", 0, false, false, "0", "Seconds to wait for the remote user interface to connect (0 = wait for ever, like the reference).");
 }
 
 const OptionSpec* Options::find(const std::string& name) const {

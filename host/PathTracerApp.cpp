@@ -57,7 +57,6 @@ void PathTracerApp::init(const Options& options) {
   samplesPerPixel = roundSamplesPerPixel(samplesPerPixel, samplesPerStep);
   for (const char* ignored : {"model", "save-exe", "load-exe", "compile-only", "defer-attach", "codelet-path", "partials-type", "available-memory-proportion"})
     if (options.given(ignored)) logging::warn("Option --{} configures the Poplar graph of the reference and has no effect here.", ignored);
-  if (options.u32("ui-port") != 0) logging::warn("The remote user interface (--ui-port) is not part of this build; rendering head-less.");
   if (!loadNifModels(options.str("assets"))) throw std::runtime_error("Could not load NIF model.");
 }
 
@@ -159,21 +158,45 @@ void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
   film.setHdr(host.data());
 }
 
+// The user interaction invalidates all rendering in progress (processUserInput + defunctState,
+// PathTracerApp.cpp:510-564). The reference swaps in a fresh host state so that it need not wait for the
+// defunct jobs; here a step is a few milliseconds, so the GPUs are simply drained before the reset.
+InterfaceServer::Status PathTracerApp::processUserInput(InterfaceServer::State& state) {
+  if (state.stop) {
+    logging::info("Rendering stopped by remote UI");
+    return InterfaceServer::Status::Stop;
+  }
+  if (state.detach) {
+    // If the Remote-UI detaches just continue rendering:
+    logging::info("Remote UI disconnected.");
+    return InterfaceServer::Status::Disconnected;
+  }
+  if (!state.newNif.empty()) {
+    // Load of a new NIF was requested:
+    logging::info("Loading NIF: {}", state.newNif);
+    if (loadNifModels(state.newNif)) {
+      b200pt_nif_desc desc = nif->descriptor();
+      for (auto& g : gpus) {
+        check(b200pt_sync(g->ctx), *g, "sync");
+        check(b200pt_upload_nif(g->ctx, &desc), *g, "init_nif_weights");
+      }
+    }
+  }
+  return InterfaceServer::Status::Restart;
+}
+
 RenderSummary PathTracerApp::execute() {
   const auto imageWidth = args->u32("width");
   const auto imageHeight = args->u32("height");
   const auto seed = args->u64("seed");
   const auto antiAliasingScale = args->f32("aa-noise-scale");
   const float fieldOfView = args->f32("fov") * (float)(M_PI / 180.0);
-  const auto exposure = args->f32("exposure");
-  const auto gamma = args->f32("gamma");
   const auto fileName = args->str("outfile");
   const auto loadBalanceEnabled = args->flag("enable-load-balancing");
   const auto saveInterval = std::max<std::uint32_t>(1, args->u32("save-interval"));
   const bool hostFilm = args->flag("host-film");
   const auto steps = samplesPerPixel / samplesPerStep;
   const float degrees = args->f32("env-map-rotation");
-  const float radians = (degrees / 360.f) * (float)(2.0 * M_PI);
   if (imageWidth == 0 || imageHeight == 0 || imageWidth > 65535 || imageHeight > 65535)
     throw std::runtime_error("Image width and height must be in 1..65535 (TraceRecord coordinates are 16 bit).");
   if (loadBalanceEnabled && !hostFilm) logging::warn("--enable-load-balancing re-deals work items between steps and needs the per-step record stream: enabling --host-film.");
@@ -190,10 +213,25 @@ RenderSummary PathTracerApp::execute() {
 
   // init_nif_weights, init_render_settings (:610-611)
   b200pt_nif_desc desc = nif->descriptor();
-  for (auto& g : gpus) {
-    check(b200pt_upload_nif(g->ctx, &desc), *g, "init_nif_weights");
-    check(b200pt_set_render_settings(g->ctx, seed, antiAliasingScale, fieldOfView, radians, samplesPerStep), *g, "init_render_settings");
+  for (auto& g : gpus) check(b200pt_upload_nif(g->ctx, &desc), *g, "init_nif_weights");
+
+  // Setup remote user interface (:618-633). Unlike the reference the state a client has not touched
+  // yet starts from the command line, with or without a client.
+  InterfaceServer::State state;
+  state.exposure = args->f32("exposure");
+  state.gamma = args->f32("gamma");
+  state.fov = fieldOfView;
+  state.envRotationDegrees = degrees;
+  state.interactiveSamples = std::max<std::uint32_t>(1, args->u32("interactive-samples"));
+  std::unique_ptr<InterfaceServer> uiServer;
+  if (const int uiPort = (int)args->u32("ui-port")) {
+    uiServer.reset(new InterfaceServer(uiPort));
+    uiServer->setInitialState(state);
+    uiServer->start((int)args->u32("ui-accept-timeout"));
+    startTime = std::chrono::steady_clock::now();
   }
+  constexpr std::size_t sampleCountReversionStep = 5;
+
   if (!recordStream)
     for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
 
@@ -206,6 +244,47 @@ RenderSummary PathTracerApp::execute() {
 
   for (std::size_t step = 1; step <= steps; ++step) {
     auto loopStartTime = std::chrono::steady_clock::now();
+
+    // Do the simple thing and restart the entire render if any state changed (:651-675):
+    if (uiServer && !uiServer->connected()) {
+      logging::warn("Remote UI connection lost: rendering continues head-less.");
+      uiServer.reset();
+    }
+    if (uiServer && uiServer->stateChanged()) {
+      state = uiServer->consumeState();
+      const auto status = processUserInput(state);
+      if (status == InterfaceServer::Status::Stop) {
+        uiServer.reset();
+        summary.steps = step - 1;
+        break;
+      }
+      if (status == InterfaceServer::Status::Disconnected) {
+        uiServer.reset();
+      } else if (status == InterfaceServer::Status::Restart) {
+        // reset_host_render_state: drain, then clear the film and the work-item accumulators
+        hostProcessing.waitForCompletion();
+        for (auto& g : gpus) { check(b200pt_sync(g->ctx), *g, "sync"); check(b200pt_film_clear(g->ctx), *g, "film_clear"); }
+        film.reset();
+        if (recordStream) work.clearActiveAccumulators();
+        summary.restarts += 1;
+        startTime = loopStartTime;
+        step = 1;
+        samplesPerStep = state.interactiveSamples;
+      }
+    } else if (uiServer && step == sampleCountReversionStep && samplesPerStep != args->u32("samples-per-step")) {
+      // No UI input for a few steps so revert to performant number of samples:
+      samplesPerStep = args->u32("samples-per-step");
+      logging::debug("Interaction stopped reverting samples per step to: {}", samplesPerStep);
+    }
+
+    // Render settings can only be updated on these steps (:677-686):
+    if (step == 1 || (uiServer && step == sampleCountReversionStep)) {
+      const float radians = (state.envRotationDegrees / 360.f) * (float)(2.0 * M_PI);
+      for (auto& g : gpus) {
+        check(b200pt_sync(g->ctx), *g, "sync");
+        check(b200pt_set_render_settings(g->ctx, seed, antiAliasingScale, state.fov, radians, samplesPerStep), *g, "init_render_settings");
+      }
+    }
 
     // Run path tracing on the GPUs (setup / path_trace / read_results, :690-694). Results go into the
     // active buffer whilst the async host task processes the last result from the inactive buffer.
@@ -241,8 +320,13 @@ RenderSummary PathTracerApp::execute() {
         if (loadBalanceEnabled && step > 1) work.allocateWorkByPathLength();
         totalRays = work.clearInactiveAccumulators();
         if (saveNow) {
-          film.saveImages(fileName, step, exposure, gamma);
-          logging::info("Saved images at step {}", step);
+          // With a UI server the full uncompressed image is transmitted at the save interval (:748-759);
+          // files are written on the final step only.
+          if (uiServer) uiServer->startSendingRawImage(film.getHdrImage(), imageWidth, imageHeight, step, step == steps);
+          if (!uiServer || step == steps) {
+            film.saveImages(fileName, step, state.exposure, state.gamma);
+            logging::info("Saved images at step {}", step);
+          }
         }
       });
     } else {
@@ -251,10 +335,12 @@ RenderSummary PathTracerApp::execute() {
         // one gather per save interval; encoding and writing the files overlaps the next steps
         hostProcessing.waitForCompletion();
         gatherDeviceFilm(film);
-        hostProcessing.run([&, step]() {
-          film.saveImages(fileName, step, exposure, gamma);
-          logging::info("Saved images at step {}", step);
-        });
+        if (uiServer) uiServer->startSendingRawImage(film.getHdrImage(), imageWidth, imageHeight, step, step == steps);
+        if (!uiServer || step == steps)
+          hostProcessing.run([&, step]() {
+            film.saveImages(fileName, step, state.exposure, state.gamma);
+            logging::info("Saved images at step {}", step);
+          });
       }
     }
 
@@ -263,9 +349,18 @@ RenderSummary PathTracerApp::execute() {
     const double pixelSamplesPerStep = (double)imageWidth * imageHeight * samplesPerStep;
     logging::info("Completed render step {}/{} in {} seconds (Samples/sec {}) (Rays/sec {})", step, steps, secs, pixelSamplesPerStep / secs,
                   (recordStream ? totalRays : stepRays) / secs);
+    if (uiServer) {
+      // exposure and gamma are applied by the client to the raw image: pick up the latest for the files
+      const auto latest = uiServer->getState();
+      state.exposure = latest.exposure; state.gamma = latest.gamma;
+      uiServer->sendPreviewImage({}, imageWidth, imageHeight);
+      uiServer->updateProgress((int)step, (int)steps);
+      uiServer->updateSampleRate((float)(pixelSamplesPerStep / secs), (float)((recordStream ? totalRays : stepRays) / secs));
+    }
   }
 
   hostProcessing.waitForCompletion();
+  if (uiServer) { uiServer->waitForRawImage(); uiServer.reset(); }
   if (recordStream && loadBalanceEnabled) {
     // the inactive list was re-dealt for a step that never ran: nothing to do, the film is complete
   }

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "AccumulatedImage.hpp"
+#include "InterfaceServer.hpp"
 #include "LoadBalancer.hpp"
 #include "NifAssets.hpp"
 #include "Options.hpp"
@@ -20,6 +21,7 @@ struct RenderSummary {
   double samplesPerSec = 0.0;
   std::size_t steps = 0;
   std::size_t samplesPerPixel = 0;
+  std::size_t restarts = 0;            // renders restarted by the remote UI
   std::uint64_t paths = 0, escaped = 0, rays = 0;
   double traceMs = 0.0, nifMs = 0.0, deviceMs = 0.0;
   std::string lastError;
@@ -51,4 +53,6 @@ private:
   void createContexts(std::uint32_t width, std::uint32_t height, std::size_t itemsPerGpu);
   void check(int rc, Gpu& g, const char* what);
   void gatherDeviceFilm(AccumulatedImage& film);
+  /// Stop / detach / (reload NIF and) restart decision for a changed UI state (PathTracerApp.cpp:531-564).
+  InterfaceServer::Status processUserInput(InterfaceServer::State& state);
 };

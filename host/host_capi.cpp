@@ -140,4 +140,47 @@ int b200host_h5_list(const char* file, const char* group, char* out, size_t cap)
   return guarded([&] { hdf5::File f(file); std::string s; for (auto& n : f.list(group)) s += n + "\n"; copyOut(s, out, cap); });
 }
 
+// Remote UI: serves one client on <port> through the same decisions as PathTracerApp::execute, with a
+// synthetic "render": every step takes stepMs, the film value of every pixel is (fov, envRotationDegrees,
+// interactiveSamples) in B,G,R (so the client sees R = interactiveSamples, G = rotation, B = fov) times the
+// step number. Writes "steps=..;restarts=..;stopped=..;detached=..;exposure=..;gamma=..;fov=..;rot=..;nif=..;isamples=..".
+int b200host_ui_session(int port, uint32_t w, uint32_t h, uint32_t steps, uint32_t saveInterval, uint32_t stepMs, int acceptTimeoutS, char* out, size_t cap) {
+  return guarded([&] {
+    std::unique_ptr<InterfaceServer> ui(new InterfaceServer(port));
+    InterfaceServer::State state;
+    state.fov = 1.f; state.interactiveSamples = 8;
+    ui->setInitialState(state);
+    ui->start(acceptTimeoutS);
+    AccumulatedImage film(w, h);
+    std::vector<float> px((size_t)w * h * 3);
+    size_t restarts = 0, done = 0;
+    bool stopped = false, detached = false;
+    std::string lastNif;
+    for (uint32_t step = 1; step <= steps; ++step) {
+      if (ui && !ui->connected()) ui.reset();
+      if (ui && ui->stateChanged()) {
+        state = ui->consumeState();
+        if (state.stop) { stopped = true; ui.reset(); break; }
+        if (state.detach) { detached = true; ui.reset(); }
+        else { if (!state.newNif.empty()) lastNif = state.newNif; film.reset(); restarts++; step = 1; }
+      }
+      std::this_thread::sleep_for(std::chrono::milliseconds(stepMs));
+      for (size_t i = 0; i < px.size(); i += 3) { px[i] = state.fov * step; px[i + 1] = state.envRotationDegrees * step; px[i + 2] = (float)state.interactiveSamples * step; }
+      film.setHdr(px.data());
+      done = step;
+      if (ui) {
+        const auto latest = ui->getState();
+        state.exposure = latest.exposure; state.gamma = latest.gamma;
+        if (step % saveInterval == 0 || step == steps) ui->startSendingRawImage(film.getHdrImage(), w, h, step, step == steps);
+        ui->updateProgress((int)step, (int)steps);
+        ui->updateSampleRate(1000.f * step, 2000.f * step);
+      }
+    }
+    if (ui) { ui->waitForRawImage(); ui.reset(); }
+    char buf[512];
+    std::snprintf(buf, sizeof(buf), "steps=%zu;restarts=%zu;stopped=%d;detached=%d;exposure=%.9g;gamma=%.9g;fov=%.9g;rot=%.9g;nif=%s;isamples=%u", done, restarts,
+                  (int)stopped, (int)detached, state.exposure, state.gamma, state.fov, state.envRotationDegrees, lastNif.c_str(), state.interactiveSamples);
+    copyOut(buf, out, cap);
+  });
+}
 } // extern "C"

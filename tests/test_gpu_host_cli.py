@@ -82,3 +82,93 @@ def test_cli_error_contract(cli, tmp_path, nif_model):
     assert r.returncode != 0 and "Invalid AA noise type: pink" in r.stderr
     r = subprocess.run([cli, "-o", str(tmp_path / "x.png"), "--assets", assets, "-w", "32", "-h", "32", "--roulette-depth", "0"], capture_output=True, text=True)
     assert r.returncode != 0 and "roulette_depth" in r.stderr
+
+
+def _free_port():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _rrmse(a, b):
+    return float(np.sqrt(np.mean((a - b) ** 2)) / np.mean(b))
+
+
+def test_cli_remote_ui_session(cli, nif_model, tmp_path):
+    """--ui-port: a client of the reference's wire protocol steers the render (PathTracerApp.cpp:618-675,726-759):
+    it receives progress, sample rates and the raw image; a new field of view restarts the render with the new
+    camera; stop ends the process cleanly."""
+    import cv2
+    from ui_client import UiClient
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    w, h = 96, 64
+    assets = _assets(tmp_path, nif_model)
+    base = [cli, "--assets", assets, "-w", str(w), "-h", str(h), "--samples-per-step", "128", "--seed", "3"]
+    refs = {}
+    for fov in (90, 50):                                   # head-less references of the two cameras
+        out = str(tmp_path / f"ref{fov}.png")
+        r = subprocess.run(base + ["-o", out, "-s", "32768", "--save-interval", "256", "--fov", str(fov), "--env-map-rotation", "30" if fov == 50 else "0"],
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        refs[fov] = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED).astype(np.float64)[:, :, ::-1]      # -> R,G,B
+    assert _rrmse(refs[50], refs[90]) > 0.2
+
+    port = _free_port()
+    out = str(tmp_path / "ui.png")
+    p = subprocess.Popen(base + ["-o", out, "-s", str(128 * 1000000), "--save-interval", "16", "--ui-port", str(port), "--ui-accept-timeout", "120"],
+                         stderr=subprocess.PIPE, text=True)
+    try:
+        c = UiClient(port, connect_timeout=120)
+        assert c.wait(lambda c: len(c.images) >= 1 and len(c.rates) >= 16, timeout=120)
+        first = c.images[0].astype(np.float64)
+        assert first.shape == (h, w, 3)
+        assert _rrmse(first, refs[90]) < 0.08, _rrmse(first, refs[90])
+        assert c.rates[-1][0] > 0 and c.rates[-1][1] > c.rates[-1][0]          # rays/s > paths/s
+        assert 0 < c.progress[-1] < 1e-3
+        c.send_float("exposure", 1.0)                                         # no restart
+        c.send_float("fov", 50.0)
+        c.send_float("env_rotation", 30.0)
+        assert c.wait(lambda c: any(_rrmse(i.astype(np.float64), refs[50]) < 0.08 for i in c.images[-2:]), timeout=120), \
+            [_rrmse(i.astype(np.float64), refs[50]) for i in c.images[-3:]]
+        with c.lock:
+            drops = sum(1 for a, b in zip(c.progress, c.progress[1:]) if b < a)
+        assert 1 <= drops <= 2
+        c.send_bool("stop")
+        rc = p.wait(timeout=60)
+        err = p.stderr.read()
+        assert rc == 0, err[-2000:]
+        assert "Rendering stopped by remote UI" in err and "Render finished" in err
+        c.close()
+    finally:
+        if p.poll() is None:
+            p.kill()
+
+
+def test_cli_remote_ui_runs_to_completion_and_saves(cli, nif_model, tmp_path):
+    """With a client attached the files are written on the final step and the last raw image is that EXR."""
+    import cv2
+    from ui_client import UiClient
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    w, h = 64, 48
+    assets = _assets(tmp_path, nif_model)
+    port = _free_port()
+    out = str(tmp_path / "ui.png")
+    p = subprocess.Popen([cli, "--assets", assets, "-w", str(w), "-h", str(h), "-s", "96", "--samples-per-step", "8", "--save-interval", "5", "-o", out,
+                          "--ui-port", str(port), "--ui-accept-timeout", "120", "--host-film"], stderr=subprocess.PIPE, text=True)
+    try:
+        c = UiClient(port, connect_timeout=120)
+        rc = p.wait(timeout=120)
+        err = p.stderr.read()
+        assert rc == 0, err[-2000:]
+        assert c.closed.wait(10)
+        assert "Saved images at step 12" in err and "Saved images at step 5" not in err
+        assert len(c.images) >= 1 and abs(c.progress[-1] - 1.0) < 1e-6
+        exr = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED)
+        np.testing.assert_allclose(c.images[-1][:, :, ::-1], exr, rtol=2e-3, atol=1e-6)
+        c.close()
+    finally:
+        if p.poll() is None:
+            p.kill()

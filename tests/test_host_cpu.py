@@ -323,3 +323,124 @@ def test_cli_binary_fails_loudly_without_gpu(tmp_path):
     assert r.returncode != 0
     assert "no CUDA device" in r.stderr and "no CPU path" in r.stderr
     assert not (tmp_path / "o.png").exists()
+
+
+# ---- remote user interface (src/InterfaceServer.hpp, external/packetcomms) --------------------------------
+
+def _free_port():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _ui_session(host, port, result, **kw):
+    out = C.create_string_buffer(1024)
+    rc = host.b200host_ui_session(port, kw.get("w", 12), kw.get("h", 7), kw.get("steps", 40), kw.get("save", 4), kw.get("step_ms", 20),
+                                  kw.get("accept", 20), out, len(out))
+    result["rc"] = rc
+    result["err"] = host.b200host_last_error().decode() if rc else ""
+    result["out"] = dict(kv.split("=", 1) for kv in out.value.decode().split(";")) if rc == 0 else {}
+
+
+def test_ui_protocol_progress_image_restart_and_stop(host):
+    """A client speaking the packetcomms wire format gets Hello, progress, sample rates and the raw image row by row
+    (B,G,R -> R,G,B, divided by the step); changing fov / rotation / interactive samples / NIF restarts the render,
+    exposure and gamma do not; stop ends it (InterfaceServer.hpp:113-176,270-331, PathTracerApp.cpp:531-564,651-675)."""
+    import threading
+    from ui_client import HELLO, UiClient
+    port, res = _free_port(), {}
+    t = threading.Thread(target=_ui_session, args=(host, port, res), kwargs=dict(steps=100000, save=3))
+    t.start()
+    c = UiClient(port)
+    assert c.wait(lambda c: len(c.images) >= 1 and len(c.progress) >= 3)
+    assert c.control[0] == HELLO
+    img = c.images[0]
+    assert img.shape == (7, 12, 3)
+    # film = (fov, rot, isamples) * step in B,G,R; sent as R,G,B / step -> (isamples, rot, fov) = (8, 0, 1)
+    np.testing.assert_array_equal(img, np.broadcast_to(np.float32([8, 0, 1]), img.shape))
+    assert c.rates[0] == (1000.0, 2000.0)
+    assert abs(c.progress[1] - 2 / 100000) < 1e-9
+
+    # tone-mapping parameters do not restart
+    c.send_float("exposure", 1.5)
+    c.send_float("gamma", 1.8)
+    n = len(c.progress)
+    assert c.wait(lambda c: len(c.progress) >= n + 3)
+    assert c.progress[-1] > c.progress[n - 1]
+    # view parameters restart: progress drops back to step 1 and the image shows the new state
+    c.send_float("fov", 180.0)
+    c.send_float("env_rotation", 45.0)
+    c.send_u32("interactive_samples", 3)
+    c.send_string("load_nif", "/some/where/assets.extra")
+    assert c.wait(lambda c: any(np.allclose(i[0, 0], [3, 45, np.float32(np.pi)]) for i in c.images))
+    with c.lock:
+        drops = sum(1 for a, b in zip(c.progress, c.progress[1:]) if b < a)
+    assert 1 <= drops <= 4
+    c.send_bool("stop")
+    t.join(30)
+    assert not t.is_alive() and res["rc"] == 0, res
+    o = res["out"]
+    assert o["stopped"] == "1" and o["detached"] == "0" and 1 <= int(o["restarts"]) <= 4
+    assert float(o["exposure"]) == 1.5 and abs(float(o["gamma"]) - 1.8) < 1e-6
+    assert abs(float(o["fov"]) - np.pi) < 1e-6 and float(o["rot"]) == 45.0 and o["isamples"] == "3"
+    assert o["nif"] == "/some/where/assets.extra"
+    assert c.closed.wait(10)
+    c.close()
+
+
+def test_ui_detach_and_lost_connection_continue_headless(host):
+    import threading
+    from ui_client import UiClient
+    for how in ("detach", "hangup"):
+        port, res = _free_port(), {}
+        t = threading.Thread(target=_ui_session, args=(host, port, res), kwargs=dict(steps=25, save=5, step_ms=10))
+        t.start()
+        c = UiClient(port)
+        assert c.wait(lambda c: len(c.progress) >= 2)
+        if how == "detach":
+            c.send_bool("detach")
+            assert c.closed.wait(10)
+        c.close()
+        t.join(30)
+        assert not t.is_alive() and res["rc"] == 0, res
+        assert res["out"]["steps"] == "25" and res["out"]["stopped"] == "0"
+        assert res["out"]["detached"] == ("1" if how == "detach" else "0")
+
+
+def test_ui_heartbeat_bad_hello_and_accept_timeout(host):
+    import socket
+    import struct
+    import threading
+    from ui_client import HEARTBEAT, UiClient
+    # no client: start() gives up after the timeout with an error (the reference waits for ever)
+    res = {}
+    _ui_session(host, _free_port(), res, accept=1)
+    assert res["rc"] != 0 and "no client connected" in res["err"]
+    # an idle link carries a heart beat every second (PacketMuxer.cpp:140-160)
+    port, res = _free_port(), {}
+    t = threading.Thread(target=_ui_session, args=(host, port, res), kwargs=dict(steps=2, save=100, step_ms=1400))
+    t.start()
+    c = UiClient(port)
+    assert c.wait(lambda c: HEARTBEAT in c.control, timeout=10)
+    t.join(30)
+    c.close()
+    assert res["rc"] == 0 and res["out"]["steps"] == "2"
+    # a peer that does not start with Hello is dropped; the render carries on head-less
+    port, res = _free_port(), {}
+    t = threading.Thread(target=_ui_session, args=(host, port, res), kwargs=dict(steps=10, save=100, step_ms=20))
+    t.start()
+    s = None
+    for _ in range(200):
+        try:
+            s = socket.create_connection(("127.0.0.1", port), timeout=1.0)
+            break
+        except OSError:
+            import time
+            time.sleep(0.05)
+    s.sendall(struct.pack(">II", 9, 4) + struct.pack("<f", 30.0))      # fov before Hello
+    t.join(30)
+    s.close()
+    assert res["rc"] == 0 and res["out"]["steps"] == "10" and res["out"]["restarts"] == "0"
