@@ -33,6 +33,42 @@ std::vector<uint8_t> deflateAll(const uint8_t* data, size_t n, int level) {
   return out;
 }
 
+// zlib stream of `data`, deflated as independent bands on all cores (the pigz construction): every band is a raw
+// deflate stream ended on a byte boundary by Z_SYNC_FLUSH, the last one by Z_FINISH; the Adler-32 of the whole is
+// combined from the bands'. Small inputs take the single-stream path.
+std::vector<uint8_t> deflateParallel(const uint8_t* data, size_t n, int level, size_t bandBytes) {
+  const size_t bands = (n + bandBytes - 1) / bandBytes;
+  if (bands < 2) return deflateAll(data, n, level);
+  std::vector<std::vector<uint8_t>> parts(bands);
+  std::vector<uLong> adlers(bands);
+  bool failed = false;
+#pragma omp parallel for schedule(dynamic)
+  for (long b = 0; b < (long)bands; ++b) {
+    const size_t off = (size_t)b * bandBytes, len = std::min(bandBytes, n - off);
+    z_stream zs{};
+    if (deflateInit2(&zs, level, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY) != Z_OK) { failed = true; continue; }
+    auto& out = parts[(size_t)b];
+    out.resize(deflateBound(&zs, (uLong)len) + 16);
+    zs.next_in = const_cast<Bytef*>(data + off); zs.avail_in = (uInt)len;
+    zs.next_out = out.data(); zs.avail_out = (uInt)out.size();
+    const bool last = (size_t)b + 1 == bands;
+    const int rc = deflate(&zs, last ? Z_FINISH : Z_SYNC_FLUSH);
+    if ((last && rc != Z_STREAM_END) || (!last && (rc != Z_OK || zs.avail_in != 0))) failed = true;
+    out.resize(out.size() - zs.avail_out);
+    deflateEnd(&zs);
+    adlers[(size_t)b] = adler32(adler32(0L, Z_NULL, 0), data + off, (uInt)len);
+  }
+  if (failed) throw std::runtime_error("zlib deflate failed");
+  std::vector<uint8_t> out = {0x78, 0x5e};            // CM 8, 32 K window, FLEVEL 1; (0x785e % 31) == 0
+  uLong adler = adler32(0L, Z_NULL, 0);
+  for (size_t b = 0; b < bands; ++b) {
+    out.insert(out.end(), parts[b].begin(), parts[b].end());
+    adler = adler32_combine(adler, adlers[b], (z_off_t)std::min(bandBytes, n - b * bandBytes));
+  }
+  putBe32(out, (uint32_t)adler);
+  return out;
+}
+
 std::vector<uint8_t> readFile(const std::string& path) {
   std::ifstream f(path, std::ios::binary);
   if (!f) throw std::runtime_error("Could not open file: '" + path + "'");
@@ -74,7 +110,8 @@ void writePng(const std::string& path, const uint8_t* bgr8, uint32_t width, uint
   if (!width || !height) throw std::runtime_error("writePng: empty image");
   const size_t stride = (size_t)width * 3 + 1;
   std::vector<uint8_t> raw(stride * height);
-  for (uint32_t y = 0; y < height; ++y) {
+#pragma omp parallel for
+  for (long y = 0; y < (long)height; ++y) {
     uint8_t* dst = raw.data() + y * stride;
     *dst++ = 0;                                         // filter type 0 (None)
     const uint8_t* src = bgr8 + (size_t)y * width * 3;
@@ -85,7 +122,7 @@ void writePng(const std::string& path, const uint8_t* bgr8, uint32_t width, uint
   putBe32(ihdr, width); putBe32(ihdr, height);
   ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);   // 8-bit, RGB, deflate, adaptive, no interlace
   pngChunk(out, "IHDR", ihdr.data(), ihdr.size());
-  const std::vector<uint8_t> z = deflateAll(raw.data(), raw.size(), 3);
+  const std::vector<uint8_t> z = deflateParallel(raw.data(), raw.size(), 3, stride * std::max<size_t>(1, (512u << 10) / stride));
   pngChunk(out, "IDAT", z.data(), z.size());
   pngChunk(out, "IEND", nullptr, 0);
   writeFile(path, out);

@@ -165,7 +165,7 @@ def test_film_accumulate_and_tonemap_follow_accumulated_image(host, tmp_path):
     np.testing.assert_array_equal(exr, scaled)
 
 
-@pytest.mark.parametrize("w,h", [(1, 1), (16, 16), (17, 33), (640, 37)])
+@pytest.mark.parametrize("w,h", [(1, 1), (16, 16), (17, 33), (640, 37), (1104, 1000)])     # the last one takes the multi-band deflate
 def test_png_exr_round_trip_and_interop(host, tmp_path, w, h):
     import cv2
     os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
