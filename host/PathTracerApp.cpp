@@ -120,6 +120,25 @@ void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, st
   logging::info("Created {} GPU context(s): {}", gpus.size(), b200pt_version());
 }
 
+// Communicators and staging buffers of the film gather; created before the render starts so that the first save
+// interval does not pay for ncclCommInitAll.
+void PathTracerApp::initFilmGather(std::size_t n) {
+  auto cuda = [](cudaError_t e, const char* what) { if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e)); };
+  auto nccl = [](ncclResult_t r, const char* what) { if (r != ncclSuccess) throw std::runtime_error(std::string(what) + ": " + ncclGetErrorString(r)); };
+  gather.reset(new FilmGather());
+  std::vector<int> devs;
+  for (auto& g : gpus) devs.push_back(g->device);
+  gather->comms.assign(gpus.size(), nullptr);
+  nccl(ncclCommInitAll(gather->comms.data(), (int)gpus.size(), devs.data()), "ncclCommInitAll");
+  for (auto& g : gpus) {
+    cuda(cudaSetDevice(g->device), "cudaSetDevice");
+    cuda(cudaMalloc(&g->staging, n * sizeof(float)), "cudaMalloc");
+    cuda(cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+  }
+  cuda(cudaSetDevice(gpus[0]->device), "cudaSetDevice");
+  cuda(cudaMalloc(&gpus[0]->reduced, n * sizeof(float)), "cudaMalloc");
+}
+
 // One gather of the per-GPU films per save interval. Every GPU holds a full-frame film that is zero
 // outside its own pixels, so the gather is an exact sum: ncclReduce to GPU 0 over NVLink, one D->H copy.
 void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
@@ -132,20 +151,7 @@ void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
   }
   auto cuda = [](cudaError_t e, const char* what) { if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e)); };
   auto nccl = [](ncclResult_t r, const char* what) { if (r != ncclSuccess) throw std::runtime_error(std::string(what) + ": " + ncclGetErrorString(r)); };
-  if (!gather) {
-    gather.reset(new FilmGather());
-    std::vector<int> devs;
-    for (auto& g : gpus) devs.push_back(g->device);
-    gather->comms.assign(gpus.size(), nullptr);
-    nccl(ncclCommInitAll(gather->comms.data(), (int)gpus.size(), devs.data()), "ncclCommInitAll");
-    for (auto& g : gpus) {
-      cuda(cudaSetDevice(g->device), "cudaSetDevice");
-      cuda(cudaMalloc(&g->staging, n * sizeof(float)), "cudaMalloc");
-      cuda(cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking), "cudaStreamCreate");
-    }
-    cuda(cudaSetDevice(gpus[0]->device), "cudaSetDevice");
-    cuda(cudaMalloc(&gpus[0]->reduced, n * sizeof(float)), "cudaMalloc");
-  }
+  if (!gather) initFilmGather(n);
   for (auto& g : gpus) check(b200pt_film_read_device(g->ctx, g->staging, 1.f), *g, "film_read_device");   // synchronises the context
   nccl(ncclGroupStart(), "ncclGroupStart");
   for (std::size_t i = 0; i < gpus.size(); ++i)
@@ -232,6 +238,7 @@ RenderSummary PathTracerApp::execute() {
   }
   constexpr std::size_t sampleCountReversionStep = 5;
 
+  if (!recordStream && gpus.size() > 1) initFilmGather((std::size_t)imageWidth * imageHeight * 3);
   if (!recordStream)
     for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
 
