@@ -193,6 +193,41 @@ enum {
 };
 int b200pt_kat(b200pt_ctx* ctx, int op, size_t n, const float* in, int in_stride, float* out, int out_stride);
 
+/* ---- second built-in scene: the Cornell box of external/light -------------------
+ * Replaces the render loop of the reference's stand-alone CPU program external/light/src/trace.cpp
+ * (scene :168-216, options :19-35, pixel loop :246-262; path loop trace.hpp:8-107). No context and no
+ * NIF: paths end on emitters. Field defaults in comments are the reference's option defaults. */
+enum { B200PT_CORNELL_PIXEL_STREAMS = 0,   /* one random stream per (pixel, sample slice): the GPU schedule */
+       B200PT_CORNELL_TILE_STREAMS = 1 };  /* the reference's schedule: one jumped xoroshiro128** stream per tile job
+                                              (jobs.hpp:66-90) consumed serially -> its image for a seed, bit for bit */
+typedef struct b200pt_cornell_config {
+  uint32_t struct_size;
+  int32_t device;
+  uint32_t width, height;            /* 256 x 256 */
+  uint32_t tile_width, tile_height;  /* 16 x 16 (TILE_STREAMS only) */
+  uint32_t samples;                  /* 32 */
+  uint32_t roulette_depth;           /* 3 */
+  uint64_t seed;                     /* 1 */
+  float aa_noise_scale;              /* 1/700, camera-plane units */
+  float refractive_index;            /* 1.5 */
+  float stop_prob;                   /* 0.2 */
+  float epsilon;                     /* FLT_EPSILON (light.cpp:5) */
+  float intersection_epsilon;        /* 1e-5 (light.cpp:9) */
+  int32_t rng_mode;                  /* B200PT_CORNELL_* */
+} b200pt_cornell_config;
+typedef struct b200pt_cornell_stats {
+  uint64_t total_ray_casts;          /* sum of path depths (trace.cpp:301-306) */
+  uint64_t max_path_length;
+  double device_ms;                  /* kernel time (CUDA events) */
+} b200pt_cornell_stats;
+/* rgb_host: height x width x 3 fp32, R,G,B, the mean over `samples` (Image of jobs.hpp:6; p += colour / spp). */
+int b200pt_cornell_render(const b200pt_cornell_config* cfg, float* rgb_host, b200pt_cornell_stats* stats);
+/* Parity probe: path i starts at the origin towards (cam_xy[2i], cam_xy[2i+1], -1) with the xoroshiro128** state
+ * rng_state[2i..2i+1] (advanced in place); rgb[3i..] = trace() (trace.hpp:8-107), depth[i] = its ray casts. */
+int b200pt_cornell_trace_paths(const b200pt_cornell_config* cfg, size_t n, const float* cam_xy, uint64_t* rng_state,
+                               float* rgb, uint32_t* depth);
+const char* b200pt_cornell_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,6 +17,7 @@ EXPORTS = [
     "b200pt_film_read_device", "b200pt_film_tonemap", "b200pt_set_sample_index", "b200pt_get_counters",
     "b200pt_nif_flops_per_eval", "b200pt_nif_infer", "b200pt_nif_infer_device", "b200pt_trace_wavefront",
     "b200pt_trace_fixed", "b200pt_kat",
+    "b200pt_cornell_render", "b200pt_cornell_trace_paths", "b200pt_cornell_last_error",
 ]
 
 
@@ -43,6 +44,17 @@ class Counters(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("escaped", C.c_uint64), ("path_segments", C.c_uint64),
                 ("trace_ms", C.c_double), ("nif_ms", C.c_double), ("total_ms", C.c_double),
                 ("kernel_launches", C.c_uint64), ("nif_impl_used", C.c_int32)]
+
+
+class CornellConfig(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("width", C.c_uint32), ("height", C.c_uint32),
+                ("tile_width", C.c_uint32), ("tile_height", C.c_uint32), ("samples", C.c_uint32), ("roulette_depth", C.c_uint32),
+                ("seed", C.c_uint64), ("aa_noise_scale", C.c_float), ("refractive_index", C.c_float), ("stop_prob", C.c_float),
+                ("epsilon", C.c_float), ("intersection_epsilon", C.c_float), ("rng_mode", C.c_int32)]
+
+
+class CornellStats(C.Structure):
+    _fields_ = [("total_ray_casts", C.c_uint64), ("max_path_length", C.c_uint64), ("device_ms", C.c_double)]
 
 
 def build(verbose: bool = False) -> str:
@@ -96,5 +108,8 @@ def load() -> C.CDLL:
     lib.b200pt_trace_wavefront.argtypes = [vp, u32, sz, vp, vp, vp, vp, vp]
     lib.b200pt_trace_fixed.argtypes = [vp, sz, vp, vp, u32, vp, vp, vp, vp]
     lib.b200pt_kat.argtypes = [vp, i32, sz, vp, i32, vp, i32]
+    lib.b200pt_cornell_render.argtypes = [C.POINTER(CornellConfig), vp, C.POINTER(CornellStats)]
+    lib.b200pt_cornell_trace_paths.argtypes = [C.POINTER(CornellConfig), sz, vp, vp, vp, vp]
+    lib.b200pt_cornell_last_error.restype = C.c_char_p
     _lib = lib
     return lib

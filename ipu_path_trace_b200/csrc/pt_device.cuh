@@ -91,6 +91,49 @@ __device__ __forceinline__ void tangentFrame(V3 n, V3& ax, V3& ay) {
   ay = cross(n, ax);
 }
 
+// sinf/cosf as the reference's CPU build computes them. glibc (>= 2.28) evaluates both in double: quadrant n =
+// round(x * 2/pi) taken from a 2^24-prescaled product, r = x - n*pi/2, then an odd (sin) or even (cos) polynomial of r
+// chosen by n, rounded to float once. The result is NOT the correctly rounded sine (it differs from (float)sin((double)x)
+// for 1.3 % of the arguments in [0, 2 pi]), and the device's own sinf is 1-2 ulp, so neither reproduces the reference;
+// this does, for every float in [0, 2 pi] (checked exhaustively on the host against glibc 2.39). Valid for |x| < 120.
+__device__ __forceinline__ float glibcSinCosPoly(double x, double x2, bool flip, int n) {
+  // the second table of the routine is the first with the cosine coefficients negated
+  const double sg = flip ? -1.0 : 1.0;
+  if ((n & 1) == 0) {
+    const double x3 = x * x2;
+    const double s1 = 0x1.1107605230bc4p-7 + x2 * -0x1.994eb3774cf24p-13;
+    const double x7 = x3 * x2;
+    const double s = x + x3 * -0x1.555545995a603p-3;
+    return (float)(s + x7 * s1);
+  }
+  const double x4 = x2 * x2;
+  const double c2 = sg * -0x1.6c087e89a359dp-10 + x2 * (sg * 0x1.99343027bf8c3p-16);
+  const double c1 = sg * 0x1p0 + x2 * (sg * -0x1.ffffffd0c621cp-2);
+  const double x6 = x4 * x2;
+  const double c = c1 + x4 * (sg * 0x1.55553e1068f19p-5);
+  return (float)(c + x6 * c2);
+}
+__device__ __forceinline__ void glibcSinCosf(float y, float& sinOut, float& cosOut) {
+  const double x = (double)y;
+  const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ffu;
+  if (top < ((0x3f490fdbu >> 20) & 0x7ffu)) {                 // |y| < pi/4 by exponent+top mantissa bits, as glibc tests it
+    const double x2 = x * x;
+    if (top < ((0x39800000u >> 20) & 0x7ffu)) { sinOut = y; cosOut = 1.f; return; }      // |y| < 2^-12
+    sinOut = glibcSinCosPoly(x, x2, false, 0);
+    cosOut = glibcSinCosPoly(x, x2, false, 1);
+    return;
+  }
+  const double r = x * 0x1.45F306DC9C883p+23;                  // 2/pi * 2^24
+  const int n = (__double2int_rz(r) + 0x800000) >> 24;
+  const double xr = x - (double)n * 0x1.921FB54442D18p0;
+  const double x2 = xr * xr;
+  const int ns = n & 3, nc = (n + 1) & 3;
+  const double ss = (ns == 1 || ns == 2) ? -1.0 : 1.0;         // sign table {1, -1, -1, 1}
+  const double sc = (nc == 1 || nc == 2) ? -1.0 : 1.0;
+  sinOut = glibcSinCosPoly(xr * ss, x2, (ns & 2) != 0, n);
+  cosOut = glibcSinCosPoly(xr * sc, x2, (nc & 2) != 0, n ^ 1);
+}
+
 // sdf.hpp:8-31 diffuse() with hemisphere() light.hpp:223-228. Returns the record weight
 // cos(theta) * 0.1 * rr (SURVEY 8a quirk iv: not a normalised Lambert estimator; kept).
 __device__ __forceinline__ float sampleDiffuse(V3& dir, V3 n, float rr, float u1, float u2) {
@@ -98,13 +141,11 @@ __device__ __forceinline__ float sampleDiffuse(V3& dir, V3 n, float rr, float u1
   tangentFrame(n, ax, ay);
   const float r = sqrtf(1.f - u1 * u1);
   const float phi = 2.f * kPi * u2;
-  // glibc's sinf/cosf (what the reference's CPU build and the oracle call) evaluate in double and
-  // round once, i.e. they are correctly rounded in all but ~1e-7 of cases; the device's sinf/cosf
-  // are 1-2 ulp. The thin clear-coat shell (radii .4 / .4001, codelets.cpp:126-131) amplifies a
-  // last-bit difference into a different hit sequence, so take the double route here as well.
-  double sd, cd;
-  sincos((double)phi, &sd, &cd);
-  const V3 h = v3((float)cd * r, (float)sd * r, u1);
+  // The thin clear-coat shell (radii .4 / .4001, codelets.cpp:126-131) and the closed Cornell box amplify a last-bit
+  // difference in the sampled direction into a different hit sequence, so sinf/cosf must be the reference's, bit for bit.
+  float sp, cp;
+  glibcSinCosf(phi, sp, cp);
+  const V3 h = v3(cp * r, sp * r, u1);
   dir = v3(dot(v3(ax.x, ay.x, n.x), h), dot(v3(ax.y, ay.y, n.y), h), dot(v3(ax.z, ay.z, n.z), h));
   return dot(dir, n) * .1f * rr;
 }

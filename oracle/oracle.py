@@ -371,3 +371,37 @@ def make_worklist(width: int, height: int) -> np.ndarray:
     items["u"] = uu
     items["v"] = vv
     return items
+
+
+class CornellReference:
+    """The reference's CPU tracer of the Cornell-box scene, compiled unmodified (oracle/_ref/libref_cornell.so,
+    external/light/src/trace.hpp). TEST INFRASTRUCTURE ONLY."""
+
+    PATH = os.path.join(HERE, "_ref", "libref_cornell.so")
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(CornellReference.PATH)
+
+    def __init__(self):
+        self.lib = C.CDLL(self.PATH)
+
+    def trace_paths(self, cam_xy, rng_state, refractive_index=1.5, roulette_depth=3, stop_prob=0.2,
+                    epsilon=float(np.finfo(np.float32).eps), intersection_epsilon=1e-5):
+        cam = np.ascontiguousarray(cam_xy, np.float32)
+        state = np.array(rng_state, np.uint64, copy=True, order="C")
+        n = cam.shape[0]
+        rgb = np.zeros((n, 3), np.float32)
+        depth = np.zeros(n, np.uint32)
+        self.lib.ref_cornell_trace_paths(C.c_size_t(n), _ptr(cam), _ptr(state), C.c_float(refractive_index), C.c_uint32(roulette_depth),
+                                         C.c_float(stop_prob), C.c_float(epsilon), C.c_float(intersection_epsilon), _ptr(rgb), _ptr(depth))
+        return rgb, depth, state
+
+    def render(self, width, height, tile_width, tile_height, samples, seed, aa_noise_scale=1.0 / 700, refractive_index=1.5,
+               roulette_depth=3, stop_prob=0.2, epsilon=float(np.finfo(np.float32).eps), intersection_epsilon=1e-5):
+        rgb = np.zeros((height, width, 3), np.float32)
+        stats = np.zeros(2, np.uint64)
+        self.lib.ref_cornell_render(C.c_uint32(width), C.c_uint32(height), C.c_uint32(tile_width), C.c_uint32(tile_height), C.c_uint32(samples),
+                                    C.c_uint64(seed), C.c_float(aa_noise_scale), C.c_float(refractive_index), C.c_uint32(roulette_depth),
+                                    C.c_float(stop_prob), C.c_float(epsilon), C.c_float(intersection_epsilon), _ptr(rgb), _ptr(stats))
+        return rgb, {"total_ray_casts": int(stats[0]), "max_path_length": int(stats[1])}

@@ -1,0 +1,133 @@
+"""Second built-in scene: the Cornell box of the reference's stand-alone CPU renderer
+(external/light/src/trace.cpp, trace.hpp). The oracle is that renderer compiled UNMODIFIED (oracle/_ref/libref_cornell.so)
+and the golden vectors generated from it (tests/golden/cornell.npz, tests/golden/make_cornell_golden.py). The CUDA path must
+return the reference's bits for the same xoroshiro128** streams: colours, ray-cast counts and the advanced generator state."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+ALT = dict(refractive_index=1.33, roulette_depth=2, stop_prob=0.35, epsilon=1e-6, intersection_epsilon=1e-4)
+RENDER = dict(width=40, height=28, tile_width=16, tile_height=16, samples=8, seed=7, aa_noise_scale=1.0 / 700)
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(ROOT, "tests", "golden", "cornell.npz"))
+
+
+@pytest.fixture(scope="module")
+def cref(O):
+    if not O.CornellReference.available():
+        pytest.skip("oracle/_ref/libref_cornell.so not built (needs /root/reference)")
+    return O.CornellReference()
+
+
+# ---- CPU: the fixtures are the reference's own outputs --------------------------------------------------------------
+
+def test_golden_vectors_are_the_compiled_reference(gold, cref):
+    rgb, depth, st = cref.trace_paths(gold["cam_xy"], gold["rng_state"])
+    assert np.array_equal(rgb.view(np.uint32), gold["rgb_default"].view(np.uint32))
+    assert np.array_equal(depth, gold["depth_default"]) and np.array_equal(st, gold["state_default"])
+    rgb, depth, st = cref.trace_paths(gold["cam_xy"], gold["rng_state"], **ALT)
+    assert np.array_equal(rgb.view(np.uint32), gold["rgb_alt"].view(np.uint32))
+    assert np.array_equal(depth, gold["depth_alt"]) and np.array_equal(st, gold["state_alt"])
+    img, stats = cref.render(**RENDER)
+    assert np.array_equal(img.view(np.uint32), gold["render_rgb"].view(np.uint32))
+    assert [stats["total_ray_casts"], stats["max_path_length"]] == gold["render_stats"].tolist()
+
+
+def test_golden_vectors_cover_the_scene(gold):
+    """Emitter hits through every material, roulette stops, depth-limit paths and unlit paths are all present."""
+    rgb, depth = gold["rgb_default"], gold["depth_default"]
+    lit = rgb.sum(axis=1) > 0
+    assert 0.05 < lit.mean() < 0.5 and (depth == 20).any() and (depth[lit] == 0).any() and (depth[lit] >= 5).any()
+    assert (depth[~lit] == 3).any()                       # stopped by the first roulette draw
+    assert gold["render_rgb"].shape == (28, 40, 3) and gold["render_stats"][1] <= 20
+
+
+def test_cornell_needs_the_gpu_library(lib_built):
+    """No CPU path: without a device the entry points fail with the library's message; bad arguments are rejected first."""
+    import torch
+    from ipu_path_trace_b200 import _lib, cornell
+    lib = _lib.load()
+    cfg = cornell.CornellOptions(width=8, height=8).to_c()
+    cfg.struct_size = 4
+    rgb = np.zeros((8, 8, 3), np.float32)
+    assert lib.b200pt_cornell_render(C.byref(cfg), rgb.ctypes.data, None) != 0
+    assert b"struct_size" in lib.b200pt_cornell_last_error()
+    with pytest.raises(RuntimeError, match="must be > 0"):
+        cornell.render(cornell.CornellOptions(width=0))
+    with pytest.raises(RuntimeError, match="stop_prob"):
+        cornell.render(cornell.CornellOptions(stop_prob=1.0))
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CUDA device"):
+            cornell.render(cornell.CornellOptions(width=8, height=8, samples=1))
+
+
+# ---- GPU: parity through the C ABI ----------------------------------------------------------------------------------
+
+def _opts(**kw):
+    from ipu_path_trace_b200 import cornell
+    return cornell.CornellOptions(**kw)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["default", "alt"])
+def test_paths_match_the_reference_bit_for_bit(lib_built, gold, which):
+    from ipu_path_trace_b200 import cornell
+    rgb, depth, st = cornell.trace_paths(_opts(**(ALT if which == "alt" else {})), gold["cam_xy"], gold["rng_state"])
+    assert np.array_equal(depth, gold["depth_" + which])
+    assert np.array_equal(st, gold["state_" + which])
+    assert np.array_equal(rgb.view(np.uint32), gold["rgb_" + which].view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_tile_stream_render_is_the_reference_image(lib_built, gold):
+    """TILE_STREAMS reproduces trace.cpp's image for a seed: jumped per-tile streams, ragged edge tiles, p += colour / spp."""
+    from ipu_path_trace_b200 import cornell
+    img, stats = cornell.render(_opts(rng_mode=cornell.TILE_STREAMS, **RENDER))
+    assert [stats["total_ray_casts"], stats["max_path_length"]] == gold["render_stats"].tolist()
+    assert np.array_equal(img.view(np.uint32), gold["render_rgb"].view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_against_the_compiled_reference_on_fresh_inputs(lib_built, cref):
+    """Larger seeded inputs than the fixture, when the compiled reference travelled with the snapshot."""
+    from ipu_path_trace_b200 import cornell
+    rng = np.random.default_rng(99)
+    n = 200000
+    cam = rng.uniform(-1.2, 1.2, (n, 2)).astype(np.float32)
+    state = rng.integers(1, 2 ** 63, (n, 2), dtype=np.uint64)
+    want = cref.trace_paths(cam, state)
+    got = cornell.trace_paths(_opts(), cam, state)
+    for g, w in zip(got, want):
+        assert np.array_equal(g.view(np.uint32) if g.dtype == np.float32 else g, w.view(np.uint32) if w.dtype == np.float32 else w)
+    kw = dict(width=70, height=33, tile_width=8, tile_height=16, samples=5, seed=12345, aa_noise_scale=0.01)
+    wimg, wstats = cref.render(**kw)
+    img, stats = cornell.render(_opts(rng_mode=cornell.TILE_STREAMS, **kw))
+    assert np.array_equal(img.view(np.uint32), wimg.view(np.uint32))
+    assert stats["total_ray_casts"] == wstats["total_ray_casts"] and stats["max_path_length"] == wstats["max_path_length"]
+
+
+@pytest.mark.gpu
+def test_pixel_stream_render_converges_to_the_same_image(lib_built):
+    """The GPU schedule draws different random numbers: same estimator, so block means agree at high sample counts,
+    ray casts per path agree, and the image does not depend on the slice count chosen for occupancy."""
+    from ipu_path_trace_b200 import cornell
+    w, h = 64, 64
+    a, sa = cornell.render(_opts(width=w, height=h, samples=4096, seed=1))
+    b, sb = cornell.render(_opts(width=w, height=h, samples=4096, seed=2))
+    t, st = cornell.render(_opts(width=w, height=h, samples=256, seed=3, rng_mode=cornell.TILE_STREAMS))
+    blocks = lambda x: x.reshape(4, h // 4, 4, w // 4, 3).mean(axis=(1, 3))
+    rel = lambda x, y: float(np.abs(blocks(x) - blocks(y)).mean() / blocks(y).mean())
+    assert rel(a, b) < 0.05, rel(a, b)
+    assert rel(a, t) < 0.12, rel(a, t)
+    per_path = lambda s, spp: s["total_ray_casts"] / (w * h * spp)
+    assert abs(per_path(sa, 4096) - per_path(st, 256)) / per_path(st, 256) < 0.01
+    assert sa["max_path_length"] == 20 and sa["device_ms"] > 0
+    assert np.isfinite(a).all() and a.min() >= 0
