@@ -23,6 +23,8 @@ struct OptionSpec {
 class Options {
 public:
   Options();
+  /// A parser over another option table (host/trace_main.cpp: the options of external/light/src/trace.cpp).
+  explicit Options(std::vector<OptionSpec> specs) : specs_(std::move(specs)) {}
   /// Throws std::runtime_error on unknown options / missing values / missing required options,
   /// and std::runtime_error("Show help") after printing the usage when --help is given (main.cpp:43-46).
   void parse(int argc, const char* const* argv);

@@ -187,15 +187,53 @@ __device__ __forceinline__ void cameraRay(uint32_t pu, uint32_t pv, float noise0
   camY = roundToHalf(-2.f * y * s.tanHalfFov);
 }
 
+// acosf as the reference's CPU build computes it: glibc's float routine (the fdlibm rational approximation in three
+// ranges, all in binary32), which is not the correctly rounded arc cosine - (float)acos((double)x) differs from it
+// for a few percent of the arguments. Checked exhaustively on the host against glibc 2.39 for every float in [-1, 1].
+__device__ __forceinline__ float glibcAcosf(float x) {
+  const float pi = 3.1415925026e+00f, pio2Hi = 1.5707962513e+00f, pio2Lo = 7.5497894159e-08f;
+  const float p0 = 1.6666667163e-01f, p1 = -3.2556581497e-01f, p2 = 2.0121252537e-01f, p3 = -4.0055535734e-02f, p4 = 7.9153501429e-04f,
+              p5 = 3.4793309169e-05f, q1 = -2.4033949375e+00f, q2 = 2.0209457874e+00f, q3 = -6.8828397989e-01f, q4 = 7.7038154006e-02f;
+  const int32_t hx = __float_as_int(x), ix = hx & 0x7fffffff;
+  if (ix == 0x3f800000) return hx > 0 ? 0.f : pi + 2.f * pio2Lo;
+  if (ix > 0x3f800000) return __int_as_float(0x7fc00000);
+  if (ix < 0x3f000000) {                                   // |x| < 0.5
+    if (ix <= 0x32800000) return pio2Hi + pio2Lo;
+    const float z = x * x;
+    const float p = z * (p0 + z * (p1 + z * (p2 + z * (p3 + z * (p4 + z * p5)))));
+    const float q = 1.f + z * (q1 + z * (q2 + z * (q3 + z * q4)));
+    const float r = p / q;
+    return pio2Hi - (x - (pio2Lo - x * r));
+  }
+  if (hx < 0) {                                            // x < -0.5
+    const float z = (1.f + x) * .5f;
+    const float p = z * (p0 + z * (p1 + z * (p2 + z * (p3 + z * (p4 + z * p5)))));
+    const float q = 1.f + z * (q1 + z * (q2 + z * (q3 + z * q4)));
+    const float s = sqrtf(z);
+    const float r = p / q;
+    const float w = r * s - pio2Lo;
+    return pi - 2.f * (s + w);
+  }
+  const float z = (1.f - x) * .5f;                         // x > 0.5
+  const float s = sqrtf(z);
+  const float df = __int_as_float(__float_as_int(s) & 0xfffff000);
+  const float c = (z - df * df) / (s + df);
+  const float p = z * (p0 + z * (p1 + z * (p2 + z * (p3 + z * (p4 + z * p5)))));
+  const float q = 1.f + z * (q1 + z * (q2 + z * (q3 + z * q4)));
+  const float r = p / q;
+  const float w = r * s + c;
+  return 2.f * (df + w);
+}
+
 // codelets.cpp:333-347 PreProcessEscapedRays: direction -> equirectangular lookup (u vertical).
 // The reference calls acosf, and `atan2` unqualified on floats (codelets.cpp:334), which on a
 // glibc toolchain is the double overload: phi, the azimuth add, the wrap and the final scale run
 // in double and v is rounded to float once. The NIF encoding multiplies uv by up to 2^11 and
 // rounds to binary16 (NifModel.cpp:211-213), so a last-bit difference in uv can move a feature
-// argument by a whole binary16 step; hence the same precision choices here (acos in double
-// rounded once stands in for glibc's correctly-rounded acosf).
+// argument by a whole binary16 step; hence acosf is glibc's own algorithm (above) and the azimuth
+// stays in double (a 2-ulp double atan2 changes the float it rounds to about once in 10^8 rays).
 __device__ __forceinline__ void escapedUv(V3 d, float azimuth, float& u, float& v) {
-  const float theta = (float)acos((double)d.y);
+  const float theta = glibcAcosf(d.y);
   double phi = atan2((double)d.z, (double)d.x) + (double)azimuth;
   const float twoPi = 2.f * kPi;
   if (phi < 0.0) { phi += (double)twoPi; } else if (phi > (double)twoPi) { phi -= (double)twoPi; }

@@ -131,3 +131,32 @@ def test_pixel_stream_render_converges_to_the_same_image(lib_built):
     assert abs(per_path(sa, 4096) - per_path(st, 256)) / per_path(st, 256) < 0.01
     assert sa["max_path_length"] == 20 and sa["device_ms"] > 0
     assert np.isfinite(a).all() and a.min() >= 0
+
+
+@pytest.mark.gpu
+def test_cli_b200_trace_writes_the_reference_image(lib_built, gold, tmp_path):
+    """host/b200_trace = external/light's `trace` command line on the GPU: with --rng tile the EXR holds the reference's
+    radiance bit for bit and the 8-bit image is min(radiance, 255) (trace.cpp:82-98); options file and statistics as :46-54,296-310."""
+    import subprocess
+    import cv2
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "b200_trace"], check=True, capture_output=True)
+    out = str(tmp_path / "cornell.png")
+    r = subprocess.run([os.path.join(ROOT, "host", "b200_trace"), "-o", out, "-w", "40", "-h", "28", "-s", "8", "--seed", "7", "--rng", "tile", "--no-gui"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    exr = cv2.imread(out + ".exr", cv2.IMREAD_UNCHANGED)
+    assert np.array_equal(np.ascontiguousarray(exr[:, :, ::-1]).view(np.uint32), gold["render_rgb"].view(np.uint32))
+    png = cv2.imread(out, cv2.IMREAD_UNCHANGED)
+    want = np.rint(np.minimum(gold["render_rgb"][:, :, ::-1], 255.0)).astype(np.uint8)
+    assert np.array_equal(png, want)
+    total, longest = (int(x) for x in gold["render_stats"])
+    assert f"Total Rays: {total} " in r.stdout and f"Max path length: {longest}" in r.stdout and "Render time:" in r.stdout
+    opts = dict(l.split(" ", 1) for l in open(out + ".command_line_options").read().splitlines())
+    assert opts["samples"] == "8" and opts["stop-prob"] == "0.2" and opts["tile-width"] == "16" and opts["rng"] == "tile"
+    assert open(out + ".hist.txt").read().split() == [str(longest)]
+    # errors: missing output name, bad mode
+    bad = subprocess.run([os.path.join(ROOT, "host", "b200_trace"), "-w", "8"], capture_output=True, text=True)
+    assert bad.returncode != 0 and "outfile" in bad.stderr
+    bad = subprocess.run([os.path.join(ROOT, "host", "b200_trace"), "-o", out, "--rng", "other"], capture_output=True, text=True)
+    assert bad.returncode != 0 and "--rng" in bad.stderr

@@ -13,7 +13,7 @@ def _mk(lib_built, nif_model, W, H, **kw):
 
 def test_trace_fixed_matches_reference_records(lib_built, nif_model, golden, O, orc):
     """RayTraceKernel (codelets.cpp:93-227) on the reference's own inputs: escape flag and record
-    count exact; direction and throughput within 1e-5 relative."""
+    count exact for every path; direction and throughput within 1e-5 relative (the fold order differs)."""
     W, H = (int(x) for x in golden["img_wh"])
     t = _mk(lib_built, nif_model, W, H)
     t.init_render_settings()
@@ -21,7 +21,7 @@ def test_trace_fixed_matches_reference_records(lib_built, nif_model, golden, O, 
     esc_w, dir_w, thr_w, len_w = orc.path_summary(rec)
     esc, d, thr, length = t.trace_fixed(golden["img_rays"], golden["img_uniforms"], 30)
     agree = (esc == esc_w) & (length == len_w)
-    assert agree.mean() > 0.999          # sinf/cosf differ in the last ulp between libms: rare control-flow flips
+    assert agree.all()                   # every branch of every path: sinf/cosf are glibc's, bit for bit (pt_device.cuh)
     m = agree & (esc == 1)
     np.testing.assert_allclose(d[m], dir_w[m], rtol=1e-5, atol=2e-6)
     np.testing.assert_allclose(thr[m], thr_w[m], rtol=1e-5, atol=1e-7)
@@ -35,7 +35,7 @@ def test_trace_fixed_matches_reference_records(lib_built, nif_model, golden, O, 
 ])
 def test_wavefront_matches_oracle(lib_built, nif_model, O, orc, cfg):
     """Philox stream -> AA noise -> GenerateCameraRays -> path -> escaped uv, one sample, against
-    the oracle on the same counters: camera rays bit-exact, flags/lengths exact up to rare libm flips."""
+    the oracle on the same counters: camera rays bit-exact, flags/lengths exact."""
     cfg = dict(cfg)
     W, H = cfg.pop("W"), cfg.pop("H")
     s = O.Settings(width=W, height=H, seed=77, env_map_rotation_degrees=33.0, **cfg)
@@ -48,7 +48,7 @@ def test_wavefront_matches_oracle(lib_built, nif_model, O, orc, cfg):
         e2, uv2, t2, l2, cam2 = orc.trace_philox(items, sample, s)
         assert np.array_equal(cam, cam2)
         agree = (esc == e2) & (length == l2)
-        assert agree.mean() > 0.999
+        assert agree.all()
         m = agree & (esc == 1)
         np.testing.assert_allclose(uv[m], uv2[m], rtol=1e-5, atol=2e-6)
         np.testing.assert_allclose(thr[m], t2[m], rtol=1e-5, atol=1e-7)
