@@ -67,43 +67,69 @@ __device__ __forceinline__ float xoUniform01(Xo& s) { return (float)xoDouble(xoN
 __device__ __forceinline__ float xoUniformNeg1To1(Xo& s) { return (float)(2.0 * xoDouble(xoNext(s)) - 1.0); }                              // :66-68
 
 // ---- light.hpp:76-93 Plane, :95-121 Disc, :123-151 Sphere, :173-191 Scene::intersect ---------------------
-__device__ __forceinline__ int cornellClosestHit(V3& o, V3 d, V3& n, float eps, float hitEps) {
+// Branch-free: the reference's early returns become selects, so that the 32 lanes of a warp - each on its own path after
+// the first bounce - stay on one instruction stream through all 13 tests (with branches ncu showed 9 of 32 lanes active).
+// A select discards exactly what the early return skipped, so every surviving t has the reference's bits.
+__device__ __forceinline__ float cornellSphereT(V3 centre, float radius2, V3 o, V3 d) {
+  const V3 f = sub(centre, o);
+  const float tca = dot(f, d);
+  const V3 l = sub(centre, add(o, scale(d, tca)));
+  const float l2 = norm2(l);
+  // misses (discarded below) take sqrtf(1): a negative or zero argument would send the whole warp through sqrtf's slow path
+  const float thc = sqrtf(l2 <= radius2 ? radius2 - l2 : 1.f);
+  const float t0 = tca - thc, t1 = tca + thc;
+  const float lo = t0 > t1 ? t1 : t0, hi = t0 > t1 ? t0 : t1;
+  const float t = lo < 0.f ? hi : lo;
+  return (!(tca < 0.f) && l2 <= radius2 && !(t < 0.f)) ? t : 0.f;
+}
+
+__device__ __forceinline__ int cornellClosestHit(const CornellScene& sc, V3& o, V3 d, V3& n, float eps, float hitEps) {
   int best = -1;
   float bestT = __int_as_float(0x7f800000);
-#pragma unroll 1
-  for (int i = 0; i < kCornellObjects; ++i) {
+#pragma unroll
+  for (int i = 0; i < kCornellObjects; ++i) {            // fully unrolled: shapes and constant-bank offsets are compile-time
     float t;
-    const int shape = gCornell.shape[i];
-    if (shape == 0) {
-      t = hitSphere(v3(gCornell.cx[i], gCornell.cy[i], gCornell.cz[i]), gCornell.radius2[i], o, d);
+    if (i < 6) {                                         // objects 0-5 spheres, 6-11 planes, 12 disc (buildCornell)
+      t = cornellSphereT(v3(gCornell.cx[i], gCornell.cy[i], gCornell.cz[i]), gCornell.radius2[i], o, d);
     } else {
       const V3 pn = v3(gCornell.nx[i], gCornell.ny[i], gCornell.nz[i]);
       const float angle = dot(pn, d);
-      t = 0.f;
-      if (angle != 0.f) {
-        const float tt = -(dot(pn, o) + gCornell.planeD[i]) / angle;
-        if (tt > eps) {
-          if (shape == 2) t = tt;
-          else {
-            const V3 hp = add(o, scale(d, tt));
-            if (norm2(sub(hp, v3(gCornell.cx[i], gCornell.cy[i], gCornell.cz[i]))) < gCornell.radius2[i]) t = tt;
-          }
-        }
+      // A ray leaving a wall has numerator exactly 0 for that wall about half of the time (o was rounded onto it): the
+      // reference then gets t = -0/angle = +-0, a miss. 0 / x leaves the fast path of the IEEE division, so those lanes
+      // divide 1 / angle instead and are marked as misses - same outcome, no slow-path call on every bounce.
+      const float num = dot(pn, o) + gCornell.planeD[i];
+      const bool onPlane = num == 0.f;
+      const float tt = -(onPlane ? 1.f : num) / angle;
+      bool ok = !onPlane && angle != 0.f && tt > eps;
+      if (i == 12) {
+        const V3 hp = add(o, scale(d, tt));
+        ok = ok && norm2(sub(hp, v3(gCornell.cx[i], gCornell.cy[i], gCornell.cz[i]))) < gCornell.radius2[i];
       }
+      t = ok ? tt : 0.f;
     }
-    if (t > hitEps && t < bestT) { bestT = t; best = i; }
+    const bool closer = t > hitEps && t < bestT;
+    bestT = closer ? t : bestT;
+    best = closer ? i : best;
   }
   if (best >= 0) {
+    // per-lane object index: read the shared-memory copy (a constant-bank read with a divergent index is replayed per address)
     o = add(o, scale(d, bestT));
-    n = gCornell.shape[best] == 0 ? unit(sub(o, v3(gCornell.cx[best], gCornell.cy[best], gCornell.cz[best])))
-                                  : v3(gCornell.nx[best], gCornell.ny[best], gCornell.nz[best]);
+    const V3 sphereN = unit(sub(o, v3(sc.cx[best], sc.cy[best], sc.cz[best])));
+    n = best < 6 ? sphereN : v3(sc.nx[best], sc.ny[best], sc.nz[best]);
   }
   return best;
 }
 
+__device__ __forceinline__ void cornellStageScene(CornellScene& sc) {
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(&gCornell);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(&sc);
+  for (uint32_t i = threadIdx.x; i < sizeof(CornellScene) / 4; i += blockDim.x) dst[i] = src[i];
+  __syncthreads();
+}
+
 // trace.hpp:8-107 for one camera ray. The reference records one Contribution per vertex and folds them from the
 // emitter back to the camera; the same fold runs here over (weight, object) pairs so that the rounding order matches.
-__device__ __forceinline__ V3 cornellTrace(V3 dirIn, Xo& rng, const CornellParams& p, uint32_t& depthOut) {
+__device__ __forceinline__ V3 cornellTrace(const CornellScene& sc, V3 dirIn, Xo& rng, const CornellParams& p, uint32_t& depthOut) {
   float weights[kCornellMaxDepth];
   int8_t objects[kCornellMaxDepth];        // >= 0: DIFFUSE by that object's colour; -1: SPECULAR / REFRACT
   V3 o = v3(0.f, 0.f, 0.f);
@@ -119,10 +145,10 @@ __device__ __forceinline__ V3 cornellTrace(V3 dirIn, Xo& rng, const CornellParam
       rr = p.rouletteWeight;
     }
     V3 n;
-    const int hit = cornellClosestHit(o, d, n, p.eps, p.hitEps);
+    const int hit = cornellClosestHit(sc, o, d, n, p.eps, p.hitEps);
     if (hit < 0) break;
-    if (gCornell.emissive[hit]) { emitter = hit; emitWeight = rr; break; }
-    const int bsdf = gCornell.bsdf[hit];
+    if (sc.emissive[hit]) { emitter = hit; emitWeight = rr; break; }
+    const int bsdf = sc.bsdf[hit];
     if (bsdf == 0) {
       const float u1 = xoUniform01(rng);
       const float u2 = xoUniform01(rng);
@@ -143,10 +169,10 @@ __device__ __forceinline__ V3 cornellTrace(V3 dirIn, Xo& rng, const CornellParam
   V3 total = v3(0.f, 0.f, 0.f);
   if (emitter >= 0) {
     // EMIT: total += emission * weight (total is zero: the sum is exact)
-    total = add(total, scale(v3(gCornell.emr[emitter], gCornell.emg[emitter], gCornell.emb[emitter]), emitWeight));
+    total = add(total, scale(v3(sc.emr[emitter], sc.emg[emitter], sc.emb[emitter]), emitWeight));
     for (int i = (int)depth - 1; i >= 0; --i) {
       const int ob = objects[i];
-      if (ob >= 0) total = scale(mul(total, v3(gCornell.colr[ob], gCornell.colg[ob], gCornell.colb[ob])), weights[i]);
+      if (ob >= 0) total = scale(mul(total, v3(sc.colr[ob], sc.colg[ob], sc.colb[ob])), weights[i]);
       else total = scale(total, weights[i]);
     }
   }
@@ -179,11 +205,13 @@ __device__ __forceinline__ void cornellStats(uint64_t casts, uint32_t longest, u
 
 __global__ void cornell_paths_kernel(size_t n, const float* __restrict__ camXY, uint64_t* __restrict__ state, float* __restrict__ rgb,
                                      uint32_t* __restrict__ depth, CornellParams p) {
+  __shared__ CornellScene sc;
+  cornellStageScene(sc);
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   Xo rng{state[2 * i], state[2 * i + 1]};
   uint32_t dep;
-  const V3 c = cornellTrace(v3(camXY[2 * i], camXY[2 * i + 1], -1.f), rng, p, dep);
+  const V3 c = cornellTrace(sc, v3(camXY[2 * i], camXY[2 * i + 1], -1.f), rng, p, dep);
   rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
   depth[i] = dep;
   state[2 * i] = rng.s0; state[2 * i + 1] = rng.s1;
@@ -193,6 +221,8 @@ __global__ void cornell_paths_kernel(size_t n, const float* __restrict__ camXY, 
 // consume in row-major order, one sample per pass, spp passes. A job is inherently serial, so parallelism is the
 // number of tiles; this mode exists to reproduce the reference's image exactly, not for speed.
 __global__ void cornell_tiles_kernel(const uint64_t* __restrict__ jobState, float* __restrict__ film, unsigned long long* stats, CornellParams p) {
+  __shared__ CornellScene sc;
+  cornellStageScene(sc);
   const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t casts = 0;
   uint32_t longest = 0;
@@ -205,7 +235,7 @@ __global__ void cornell_tiles_kernel(const uint64_t* __restrict__ jobState, floa
         for (uint32_t c = c0; c < c1; ++c) {
           const V3 cam = cornellCameraRay(c, r, rng, p);
           uint32_t dep;
-          const V3 col = cornellTrace(cam, rng, p, dep);
+          const V3 col = cornellTrace(sc, cam, rng, p, dep);
           float* px = film + ((size_t)r * p.width + c) * 3;
           px[0] += col.x / p.sppF; px[1] += col.y / p.sppF; px[2] += col.z / p.sppF;      // p += colour / spp
           casts += dep;
@@ -217,35 +247,102 @@ __global__ void cornell_tiles_kernel(const uint64_t* __restrict__ jobState, floa
 
 // B200 schedule: one stream per (pixel, slice of the samples), seeded by splitmix64 of (seed, pixel, slice); the
 // samples of a slice are summed in registers and added to the film with one atomic per channel.
-__global__ void cornell_pixels_kernel(float* __restrict__ film, unsigned long long* stats, CornellParams p) {
+// Paths in the closed box last 0..20 bounces (6.5 on average), so a lane that traced "its" path to the end while the
+// rest of the warp waits would leave two thirds of the issue slots empty (measured: 9.4 of 32 lanes active per
+// instruction). Instead every lane runs a bounce-level state machine: one loop iteration is one bounce, and a lane whose
+// path ended starts its next sample in the same iteration. The draws of a thread keep their order, so the image is the
+// one cornellTrace would give sample by sample (tests/test_cornell.py re-derives it through b200pt_cornell_trace_paths).
+__global__ void __launch_bounds__(128) cornell_pixels_kernel(float* __restrict__ film, unsigned long long* stats, CornellParams p) {
+  __shared__ CornellScene sc;
+  cornellStageScene(sc);
   const uint64_t pixels = (uint64_t)p.width * p.height;
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t casts = 0;
   uint32_t longest = 0;
-  if (t < pixels * p.slices) {
-    // consecutive lanes take consecutive pixels of one slice: neighbouring paths stay coherent for a few bounces
-    const uint64_t pixel = t % pixels;
-    const uint32_t slice = (uint32_t)(t / pixels);
-    const uint32_t row = (uint32_t)(pixel / p.width), col = (uint32_t)(pixel % p.width);
-    Xo rng;
-    rng.s0 = splitmix64(p.seed ^ (0xd1342543de82ef95ull * (t + 1)));
-    rng.s1 = splitmix64(rng.s0);
-    const uint32_t per = (p.spp + p.slices - 1) / p.slices;
-    const uint32_t s0 = slice * per, s1 = min(s0 + per, p.spp);
-    V3 sum = v3(0.f, 0.f, 0.f);
-    for (uint32_t s = s0; s < s1; ++s) {
-      const V3 cam = cornellCameraRay(col, row, rng, p);
-      uint32_t dep;
-      const V3 c = cornellTrace(cam, rng, p, dep);
-      sum = add(sum, v3(c.x / p.sppF, c.y / p.sppF, c.z / p.sppF));
-      casts += dep;
-      longest = max(longest, dep);
+  // consecutive lanes take consecutive pixels of one slice: neighbouring paths stay coherent for a few bounces
+  const uint64_t pixel = t % pixels;
+  const uint32_t slice = (uint32_t)(t / pixels);
+  const uint32_t row = (uint32_t)(pixel / p.width), col = (uint32_t)(pixel % p.width);
+  Xo rng;
+  rng.s0 = splitmix64(p.seed ^ (0xd1342543de82ef95ull * (t + 1)));
+  rng.s1 = splitmix64(rng.s0);
+  const uint32_t per = (p.spp + p.slices - 1) / p.slices;
+  const uint32_t s0 = slice * per, s1 = min(s0 + per, p.spp);
+  uint32_t s = s0;
+  bool alive = t < pixels * p.slices && s0 < s1;
+  const bool owner = alive;
+  V3 sum = v3(0.f, 0.f, 0.f);
+  float weights[kCornellMaxDepth];
+  int8_t objects[kCornellMaxDepth];
+  V3 o = v3(0.f, 0.f, 0.f), d = v3(0.f, 0.f, -1.f);
+  uint32_t depth = 0;
+  bool fresh = true;
+  // The vote keeps the whole warp in one loop: without it the compiler threads the "path ended -> next sample" edge into
+  // a private copy of the loop head and the lanes never reconverge (measured 9.3 of 32 lanes per instruction either way).
+  while (__any_sync(0xffffffffu, alive)) {
+    if (!alive) continue;
+    if (fresh) {
+      d = unit(cornellCameraRay(col, row, rng, p));
+      o = v3(0.f, 0.f, 0.f);
+      depth = 0;
+      fresh = false;
     }
-    if (s1 > s0) {
-      float* px = film + pixel * 3;
-      if (p.slices == 1) { px[0] = sum.x; px[1] = sum.y; px[2] = sum.z; }
-      else { atomicAdd(px, sum.x); atomicAdd(px + 1, sum.y); atomicAdd(px + 2, sum.z); }
+    // one bounce of trace.hpp:30-70. The roulette draw and the intersection are issued for every live lane and their
+    // effects selected afterwards: as branches, ptxas kept the "no roulette yet" and "survived roulette" lanes on two
+    // separate copies of the intersection code (every instruction of it issued twice per iteration, 13 lanes each).
+    const bool roulette = depth >= p.rouletteDepth;
+    Xo drawn = rng;
+    const float rnd = xoUniform01(drawn);
+    rng.s0 = roulette ? drawn.s0 : rng.s0;
+    rng.s1 = roulette ? drawn.s1 : rng.s1;
+    const bool stopped = roulette && rnd <= p.stopProb;
+    const float rr = roulette ? p.rouletteWeight : 1.f;
+    V3 n, hitPoint = o;
+    const int hit = cornellClosestHit(sc, hitPoint, d, n, p.eps, p.hitEps);
+    const bool emits = !stopped && hit >= 0 && sc.emissive[hit < 0 ? 0 : hit] != 0;
+    const int emitter = emits ? hit : -1;
+    bool ended = stopped || hit < 0 || emits;
+    if (!ended) {
+      o = hitPoint;
+      const int bsdf = sc.bsdf[hit];
+      if (bsdf == 0) {
+        const float u1 = xoUniform01(rng);
+        const float u2 = xoUniform01(rng);
+        weights[depth] = sampleDiffuse(d, n, rr, u1, u2);
+        objects[depth] = (int8_t)hit;
+      } else if (bsdf == 1) {
+        sampleMirror(d, n);
+        weights[depth] = rr;
+        objects[depth] = -1;
+      } else {
+        sampleGlass(d, n, p.refractiveIndex, xoUniform01(rng));
+        weights[depth] = 1.15f * rr;
+        objects[depth] = -1;
+      }
+      depth += 1;
+      ended = depth >= (uint32_t)kCornellMaxDepth;
     }
+    if (ended) {
+      if (emitter >= 0) {          // fold from the emitter back to the camera (trace.hpp:76-104)
+        V3 total = scale(v3(sc.emr[emitter], sc.emg[emitter], sc.emb[emitter]), rr);
+        for (int i = (int)depth - 1; i >= 0; --i) {
+          const int ob = objects[i];
+          if (ob >= 0) total = scale(mul(total, v3(sc.colr[ob], sc.colg[ob], sc.colb[ob])), weights[i]);
+          else total = scale(total, weights[i]);
+        }
+        sum = add(sum, v3(total.x / p.sppF, total.y / p.sppF, total.z / p.sppF));
+      }
+      casts += depth;
+      longest = max(longest, depth);
+      s += 1;
+      fresh = true;
+      alive = s < s1;
+    }
+  }
+  if (owner) {
+    float* px = film + pixel * 3;
+    if (p.slices == 1) { px[0] = sum.x; px[1] = sum.y; px[2] = sum.z; }
+    else { atomicAdd(px, sum.x); atomicAdd(px + 1, sum.y); atomicAdd(px + 2, sum.z); }
   }
   cornellStats(casts, longest, stats);
 }

@@ -1,7 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-python scratch/parity_probe.py 2>&1 | tail -4 | tee gpurun_out/parity_probe.log
-timeout 1200 python -m pytest tests -q -m gpu 2>&1 | tail -8 | tee gpurun_out/pytest_gpu.log
-timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('bench', round(d['value']/1e9,4), 'G; trace ms', d['config']['trace_ms_per_step'], 'nif ms', d['config']['nif_ms_per_step'], 'TF', d['roofline']['achieved'])"
+timeout 900 python -m pytest tests/test_cornell.py -q -m gpu 2>&1 | tail -15 | tee gpurun_out/cornell_test.log
+CORNELL="host/b200_trace -o /tmp/cornell.png -w 1024 -h 1024 -s 256"
+timeout 300 $CORNELL > gpurun_out/cornell_cli_1024.log 2>&1 && cat gpurun_out/cornell_cli_1024.log && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:cornell_pixels -c 1 -o gpurun_out/cornell_pixels_v7 -f $CORNELL > gpurun_out/ncu_cornell.log 2>&1; echo "ncu cornell exit $?"
+host/b200_trace -o /tmp/c.png -w 1920 -h 1080 -s 1024 | tee gpurun_out/cornell_cli.log

@@ -160,3 +160,56 @@ def test_cli_b200_trace_writes_the_reference_image(lib_built, gold, tmp_path):
     assert bad.returncode != 0 and "outfile" in bad.stderr
     bad = subprocess.run([os.path.join(ROOT, "host", "b200_trace"), "-o", out, "--rng", "other"], capture_output=True, text=True)
     assert bad.returncode != 0 and "--rng" in bad.stderr
+
+
+def _splitmix64(z):
+    z = (z + np.uint64(0x9e3779b97f4a7c15))
+    z = (z ^ (z >> np.uint64(30))) * np.uint64(0xbf58476d1ce4e5b9)
+    z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94d049bb133111eb)
+    return z ^ (z >> np.uint64(31))
+
+
+def _xo_next(s0, s1):
+    rotl = lambda x, k: (x << np.uint64(k)) | (x >> np.uint64(64 - k))
+    r = rotl(s0 * np.uint64(5), 7) * np.uint64(9)
+    b = s1 ^ s0
+    return r, rotl(s0, 24) ^ b ^ (b << np.uint64(16)), rotl(b, 37)
+
+
+@pytest.mark.gpu
+def test_pixel_stream_schedule_is_the_per_path_function_sample_by_sample(lib_built):
+    """PIXEL_STREAMS runs a bounce-level state machine (a lane starts its next sample as soon as its path ends). Its image must be
+    what the parity-tested per-path entry point gives when the same per-thread stream is replayed on the host: splitmix64 seeding,
+    two jitter draws (y first), the path, next sample - bit for bit when one thread owns a pixel (slices = 1)."""
+    from ipu_path_trace_b200 import cornell
+    w, h, spp, seed, aa = 1024, 600, 3, 11, 1.0 / 700            # 614 400 pixels >= two waves of threads -> slices = 1
+    img, stats = cornell.render(_opts(width=w, height=h, samples=spp, seed=seed, aa_noise_scale=aa))
+    with np.errstate(over="ignore"):
+        t = np.arange(w * h, dtype=np.uint64)
+        s0 = _splitmix64(np.uint64(seed) ^ (np.uint64(0xd1342543de82ef95) * (t + np.uint64(1))))
+        s1 = _splitmix64(s0)
+        libm = C.CDLL("libm.so.6")
+        libm.tanf.restype = C.c_float
+        libm.tanf.argtypes = [C.c_float]
+        f = np.float32
+        tan_theta = f(libm.tanf(f(f(3.14159265358979323846) / f(2)) / f(2)))
+        col = (t % np.uint64(w)).astype(np.float32)
+        row = (t // np.uint64(w)).astype(np.float32)
+        x = col / f(w) - f(.5)
+        y = row / f(h) - f(.5)
+        base_x = f(2) * x * (f(w) / f(h)) * tan_theta
+        base_y = f(-2) * y * tan_theta
+        total = np.zeros((w * h, 3), np.float32)
+        casts = 0
+        for _ in range(spp):
+            r, s0, s1 = _xo_next(s0, s1)
+            ny = (2.0 * (((np.uint64(0x3FF) << np.uint64(52)) | (r >> np.uint64(12))).view(np.float64) - 1.0) - 1.0).astype(np.float32)
+            r, s0, s1 = _xo_next(s0, s1)
+            nx = (2.0 * (((np.uint64(0x3FF) << np.uint64(52)) | (r >> np.uint64(12))).view(np.float64) - 1.0) - 1.0).astype(np.float32)
+            cam = np.stack([base_x + nx * f(aa), base_y + ny * f(aa)], axis=1)
+            rgb, depth, st = cornell.trace_paths(_opts(), cam, np.stack([s0, s1], axis=1))
+            s0, s1 = st[:, 0].copy(), st[:, 1].copy()
+            total = total + rgb / f(spp)
+            casts += int(depth.sum())
+    assert stats["total_ray_casts"] == casts
+    assert np.array_equal(img.reshape(-1, 3).view(np.uint32), total.view(np.uint32))
