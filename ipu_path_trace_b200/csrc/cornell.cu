@@ -445,7 +445,16 @@ extern "C" {
 
 const char* b200pt_cornell_last_error(void) { return g_cornellError.c_str(); }
 
+namespace {
+struct DeviceGuard {          // the entry points select cfg->device; the caller's current device is restored on return
+  int previous = -1;
+  DeviceGuard() { if (cudaGetDevice(&previous) != cudaSuccess) previous = -1; }
+  ~DeviceGuard() { if (previous >= 0) cudaSetDevice(previous); }
+};
+}
+
 int b200pt_cornell_trace_paths(const b200pt_cornell_config* cfg, size_t n, const float* camXY, uint64_t* rngState, float* rgb, uint32_t* depth) {
+  DeviceGuard guard;
   CornellParams p;
   int rc = cornellPrepare(cfg, p);
   if (rc != B200PT_OK) return rc;
@@ -469,6 +478,7 @@ done:
 }
 
 int b200pt_cornell_render(const b200pt_cornell_config* cfg, float* rgbHost, b200pt_cornell_stats* stats) {
+  DeviceGuard guard;
   CornellParams p;
   int rc = cornellPrepare(cfg, p);
   if (rc != B200PT_OK) return rc;
