@@ -91,8 +91,14 @@ def test_escaped_uv(pt, golden, O):
     idx = np.array([i for i, _ in esc_rows]); d = np.stack([rec[i, j]["clr"] for i, j in esc_rows])
     rows = np.concatenate([d, np.full((len(idx), 1), golden["img_azimuth"])], 1)
     got = pt.kat(T.KAT_ESCAPED_UV, rows, 2)
-    np.testing.assert_allclose(got[:, 0], golden["img_u"][idx], rtol=RTOL, atol=1e-6)
-    np.testing.assert_allclose(got[:, 1], golden["img_v"][idx], rtol=RTOL, atol=1e-6)
+    # against the compiled reference (codelets.cpp:333-347 with glibc's acosf / double atan2): the same bits
+    assert np.array_equal(got[:, 0].astype(np.float32).view(np.uint32), golden["img_u"][idx].astype(np.float32).view(np.uint32))
+    assert np.array_equal(got[:, 1].astype(np.float32).view(np.uint32), golden["img_v"][idx].astype(np.float32).view(np.uint32))
+    # |d.y| = 1 + 1 ulp after normalisation: the reference's acosf gives NaN and the pixel is lost for ever; clamped here
+    edge = np.array([[1e-4, np.nextafter(np.float32(1), np.float32(2)), 0.0, 0.0], [0.0, -np.nextafter(np.float32(1), np.float32(2)), 1e-4, 0.0],
+                     [0.0, 1.0, 0.0, 0.0], [0.0, -1.0, 0.0, 0.0]], np.float32)
+    uv = pt.kat(T.KAT_ESCAPED_UV, edge, 2)
+    assert np.isfinite(uv).all() and uv[0, 0] == 0.0 and uv[2, 0] == 0.0 and abs(uv[1, 0] - 1.0) < 1e-6 and abs(uv[3, 0] - 1.0) < 1e-6
 
 
 def test_philox_bit_exact(pt, orc):
