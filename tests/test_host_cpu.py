@@ -444,3 +444,26 @@ def test_ui_heartbeat_bad_hello_and_accept_timeout(host):
     t.join(30)
     s.close()
     assert res["rc"] == 0 and res["out"]["steps"] == "10" and res["out"]["restarts"] == "0"
+
+
+def test_cornell_cli_options_and_no_cpu_path(tmp_path):
+    """host/b200_trace keeps the option table of external/light/src/trace.cpp:19-35 and, like everything else here, has no CPU path."""
+    subprocess.run(["make", "-C", HOST, "b200_trace"], check=True, capture_output=True)
+    exe = os.path.join(HOST, "b200_trace")
+    h = subprocess.run([exe, "--help"], capture_output=True, text=True)
+    for opt in ("--outfile", "--width", "--height", "--tile-width", "--tile-height", "--samples", "--refractive-index", "--roulette-depth", "--stop-prob",
+                "--aa-noise-scale", "--seed", "--epsilon", "--intersection-epsilon", "--no-gui"):
+        assert opt in h.stdout, opt
+    for short, default in (("-w [ --width ] arg (=256)", None), ("-s [ --samples ] arg (=32)", None), ("-n [ --refractive-index ] arg (=1.5)", None),
+                           ("--stop-prob arg (=0.2)", None), ("--roulette-depth arg (=3)", None), ("--tile-width arg (=16)", None)):
+        assert short in h.stdout, short
+    r = subprocess.run([exe, "-w", "8"], capture_output=True, text=True)
+    assert r.returncode != 0 and "outfile" in r.stderr
+    import torch
+    if not torch.cuda.is_available():
+        out = str(tmp_path / "c.png")
+        r = subprocess.run([exe, "-o", out, "-w", "16", "-h", "16", "-s", "2", "--no-gui"], capture_output=True, text=True)
+        assert r.returncode != 0 and "no CUDA device" in r.stderr and "no CPU path" in r.stderr
+        assert not os.path.exists(out) and not os.path.exists(out + ".exr")
+        opts = dict(l.split(" ", 1) for l in open(out + ".command_line_options").read().splitlines())
+        assert opts["width"] == "16" and opts["samples"] == "2" and opts["seed"] == "1"
