@@ -109,9 +109,10 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
   uint32_t spl = cfg->samples_per_launch;
   if (spl == 0) if (const char* e = getenv("B200PT_SPL")) spl = (uint32_t)std::max(0, std::atoi(e));    // A/B runs only
   if (spl == 0) {
-    // automatic: enough escaped rays per wavefront to fill every SM with >= 64 tiles of 128 rows,
-    // bounded so the queue stays below ~1 GiB.
-    const size_t want = (size_t)c->numSms * 64 * 128;
+    // automatic: enough escaped rays per wavefront to give every SM >= 192 tiles of 128 rows (C2 on one GPU: 4 samples
+    // per launch; measured 1, 2, 3, 4, 6 -> 1.169, 1.173, 1.179, 1.182, 1.180 G samples/s), bounded so the queue stays
+    // below ~1 GiB.
+    const size_t want = (size_t)c->numSms * 192 * 128;
     spl = (uint32_t)std::max<size_t>(1, std::min<size_t>(32, (want + cap - 1) / cap));
     while (spl > 1 && cap * spl * 24 > (size_t)1 << 30) --spl;
   }
