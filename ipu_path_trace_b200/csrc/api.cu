@@ -115,6 +115,9 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     const size_t want = (size_t)c->numSms * 192 * 128;
     spl = (uint32_t)std::max<size_t>(1, std::min<size_t>(32, (want + cap - 1) / cap));
     while (spl > 1 && cap * spl * 24 > (size_t)1 << 30) --spl;
+    // path_trace shrinks the wavefront towards 64 tiles per SM when a step would otherwise have fewer than ~32 of them
+    const size_t least = (size_t)c->numSms * 64 * 128;
+    c->samplesPerLaunchMin = (uint32_t)std::min<size_t>(spl, std::max<size_t>(1, (least + cap - 1) / cap));
   }
   c->samplesPerLaunch = spl;
   if ((e = c->recStaging.alloc(cap)) != cudaSuccess) return bail(e, "cudaMalloc");

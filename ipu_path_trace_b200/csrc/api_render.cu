@@ -97,8 +97,12 @@ int b200pt_path_trace(b200pt_ctx* c) {
   const bool ov = c->overlap;
   cudaStream_t ts = ov ? c->traceStream : c->stream;
   if (ov) CU(c, cudaStreamWaitEvent(ts, c->evBegin, 0));       // setup / film work of the main stream comes first
+  // Wavefront size: the queue capacity (192 tiles per SM), shrunk towards 64 tiles per SM to keep ~32 wavefronts per step - the first
+  // trace and the last NIF launch of a step have nothing to overlap with, and their share grows with the wavefront
+  // (8 GPUs at C2, 138 k items each: 27 samples per launch 9.32 G samples/s, 18 -> 9.33, 13 -> 9.42, 9 -> 9.50).
+  const uint32_t perLaunch = c->samplesPerLaunchMin ? std::min(c->samplesPerLaunch, std::max(c->samplesPerLaunchMin, c->samplesPerStep / 32u)) : c->samplesPerLaunch;
   for (uint32_t w = 0; done < c->samplesPerStep && c->nItems > 0; ++w) {
-    const uint32_t k = std::min(c->samplesPerLaunch, c->samplesPerStep - done);
+    const uint32_t k = std::min(perLaunch, c->samplesPerStep - done);
     const uint32_t q = ov ? (w & 1u) : 0u;
     float2* qUv = q ? c->qUvB.p : c->qUv.p;
     float4* qThr = q ? c->qThrSlotB.p : c->qThrSlot.p;

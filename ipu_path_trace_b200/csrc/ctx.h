@@ -59,7 +59,8 @@ struct b200pt_ctx {
   bool settingsSet = false;
   uint32_t samplesPerStep = 0;
   uint32_t nextSample = 0;
-  uint32_t samplesPerLaunch = 0;
+  uint32_t samplesPerLaunch = 0;      // queue capacity in samples of every item
+  uint32_t samplesPerLaunchMin = 0;   // automatic choice only (else 0): lower end of the range path_trace picks from
 
   // worklist (SoA) and accumulators
   uint32_t nItems = 0;

@@ -5,7 +5,7 @@ timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&
 timeout 300 python __graft_entry__.py smoke 2>&1 | tail -2 | tee gpurun_out/smoke.log
 timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench exit $?"; cat gpurun_out/bench_n1.json
 timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref exit $?"; cat gpurun_out/bench_ref.json
-SHORT="python bench.py --steps 1 --warmup 1 --samples-per-step 20 --no-cpu-baseline"
+SHORT="python bench.py --steps 1 --warmup 1 --samples-per-step 128 --no-cpu-baseline"
 timeout 600 $SHORT > gpurun_out/bench_short.json 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $SHORT > gpurun_out/ncu_launch.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:nif_tc -s 12 -c 1 -o gpurun_out/nif_tc_mc10_bench -f $SHORT > gpurun_out/ncu_full.log 2>&1; echo "ncu full exit $?"
