@@ -91,6 +91,7 @@ __device__ __forceinline__ void tangentFrame(V3 n, V3& ax, V3& ay) {
   ay = cross(n, ax);
 }
 
+// [host-checkable: tests/test_libm_restatement.py compiles this block with g++ and compares it with the host's libm]
 // sinf/cosf as the reference's CPU build computes them. glibc (>= 2.28) evaluates both in double: quadrant n =
 // round(x * 2/pi) taken from a 2^24-prescaled product, r = x - n*pi/2, then an odd (sin) or even (cos) polynomial of r
 // chosen by n, rounded to float once. The result is NOT the correctly rounded sine (it differs from (float)sin((double)x)
@@ -133,6 +134,8 @@ __device__ __forceinline__ void glibcSinCosf(float y, float& sinOut, float& cosO
   sinOut = glibcSinCosPoly(xr * ss, x2, (ns & 2) != 0, n);
   cosOut = glibcSinCosPoly(xr * sc, x2, (nc & 2) != 0, n ^ 1);
 }
+
+// [end host-checkable]
 
 // sdf.hpp:8-31 diffuse() with hemisphere() light.hpp:223-228. Returns the record weight
 // cos(theta) * 0.1 * rr (SURVEY 8a quirk iv: not a normalised Lambert estimator; kept).
@@ -187,6 +190,7 @@ __device__ __forceinline__ void cameraRay(uint32_t pu, uint32_t pv, float noise0
   camY = roundToHalf(-2.f * y * s.tanHalfFov);
 }
 
+// [host-checkable: tests/test_libm_restatement.py compiles this block with g++ and compares it with the host's libm]
 // acosf as the reference's CPU build computes it: glibc's float routine (the fdlibm rational approximation in three
 // ranges, all in binary32), which is not the correctly rounded arc cosine - (float)acos((double)x) differs from it
 // for a few percent of the arguments. Checked exhaustively on the host against glibc 2.39 for every float in [-1, 1].
@@ -224,6 +228,8 @@ __device__ __forceinline__ float glibcAcosf(float x) {
   const float w = r * s + c;
   return 2.f * (df + w);
 }
+
+// [end host-checkable]
 
 // codelets.cpp:333-347 PreProcessEscapedRays: direction -> equirectangular lookup (u vertical).
 // The reference calls acosf, and `atan2` unqualified on floats (codelets.cpp:334), which on a
