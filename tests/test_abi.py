@@ -29,6 +29,7 @@ def test_struct_sizes_match_header(lib_built):
     assert C.sizeof(_lib.Config) == 48
     assert C.sizeof(_lib.NifLayer) == 32
     assert C.sizeof(_lib.Counters) == 64
+    assert C.sizeof(_lib.CornellConfig) == 64 and C.sizeof(_lib.CornellStats) == 24
     assert lib_built.TRACE_RECORD.itemsize == 20
 
 
