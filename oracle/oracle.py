@@ -405,3 +405,22 @@ class CornellReference:
                                     C.c_uint64(seed), C.c_float(aa_noise_scale), C.c_float(refractive_index), C.c_uint32(roulette_depth),
                                     C.c_float(stop_prob), C.c_float(epsilon), C.c_float(intersection_epsilon), _ptr(rgb), _ptr(stats))
         return rgb, {"total_ray_casts": int(stats[0]), "max_path_length": int(stats[1])}
+
+
+class CornellOracle(CornellReference):
+    """CPU restatement of the same renderer (oracle/cornell_oracle.cpp in liboracle.so): available everywhere, pinned bit for bit
+    against CornellReference and the golden vectors by tests/test_cornell.py. TEST INFRASTRUCTURE ONLY."""
+
+    PATH = os.path.join(HERE, "liboracle.so")
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(CornellOracle.PATH)
+
+    def __init__(self):
+        lib = C.CDLL(self.PATH)
+
+        class _Renamed:          # same call signatures as the compiled reference's driver, orc_ prefix
+            ref_cornell_trace_paths = lib.orc_cornell_trace_paths
+            ref_cornell_render = lib.orc_cornell_render
+        self.lib = _Renamed

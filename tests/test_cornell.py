@@ -27,7 +27,36 @@ def cref(O):
     return O.CornellReference()
 
 
+@pytest.fixture(scope="module")
+def corc(O, orc):
+    return O.CornellOracle()          # orc has built liboracle.so
+
+
 # ---- CPU: the fixtures are the reference's own outputs --------------------------------------------------------------
+
+def test_restatement_reproduces_the_golden_vectors(gold, corc):
+    """oracle/cornell_oracle.cpp against the compiled reference's outputs: every path, the image and the statistics, bit for bit."""
+    for which, kw in (("default", {}), ("alt", ALT)):
+        rgb, depth, st = corc.trace_paths(gold["cam_xy"], gold["rng_state"], **kw)
+        assert np.array_equal(rgb.view(np.uint32), gold["rgb_" + which].view(np.uint32))
+        assert np.array_equal(depth, gold["depth_" + which]) and np.array_equal(st, gold["state_" + which])
+    img, stats = corc.render(**RENDER)
+    assert np.array_equal(img.view(np.uint32), gold["render_rgb"].view(np.uint32))
+    assert [stats["total_ray_casts"], stats["max_path_length"]] == gold["render_stats"].tolist()
+
+
+def test_restatement_equals_the_compiled_reference_on_fresh_inputs(corc, cref):
+    rng = np.random.default_rng(5)
+    n = 50000
+    cam = rng.uniform(-1.5, 1.5, (n, 2)).astype(np.float32)
+    state = rng.integers(1, 2 ** 63, (n, 2), dtype=np.uint64)
+    for kw in ({}, dict(refractive_index=1.1, roulette_depth=1, stop_prob=0.5), dict(roulette_depth=25, stop_prob=0.0)):
+        a, b = corc.trace_paths(cam, state, **kw), cref.trace_paths(cam, state, **kw)
+        assert np.array_equal(a[0].view(np.uint32), b[0].view(np.uint32)) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    kw = dict(width=33, height=21, tile_width=7, tile_height=5, samples=3, seed=99, aa_noise_scale=0.02)
+    (ia, sa), (ib, sb) = corc.render(**kw), cref.render(**kw)
+    assert np.array_equal(ia.view(np.uint32), ib.view(np.uint32)) and sa == sb
+
 
 def test_golden_vectors_are_the_compiled_reference(gold, cref):
     rgb, depth, st = cref.trace_paths(gold["cam_xy"], gold["rng_state"])
@@ -96,8 +125,9 @@ def test_tile_stream_render_is_the_reference_image(lib_built, gold):
 
 
 @pytest.mark.gpu
-def test_against_the_compiled_reference_on_fresh_inputs(lib_built, cref):
-    """Larger seeded inputs than the fixture, when the compiled reference travelled with the snapshot."""
+def test_against_the_oracle_on_fresh_inputs(lib_built, corc):
+    """Larger seeded inputs than the fixture, against the CPU restatement (itself pinned to the compiled reference above)."""
+    cref = corc
     from ipu_path_trace_b200 import cornell
     rng = np.random.default_rng(99)
     n = 200000
