@@ -100,6 +100,8 @@ static void forwardOne(const std::vector<LayerF32>& ls, const Nif& nif, const st
   }
 }
 
+int nifForwardFast(const Nif* nif, int n, const float* u, const float* v, float* bgr);   // nif_fast.cpp (timing only)
+
 } // namespace orc
 
 using namespace orc;
@@ -115,9 +117,11 @@ void orc_nif_encode(int n, const float* u, const float* v, int E, std::uint16_t*
   for (int i = 0; i < n; ++i) encodeFeatures(u[i], v[i], E, features + (std::size_t)i * 4 * E);
 }
 
-// bgr: n x 3 fp32 in the network's channel order (B,G,R). mode 0 ref-faithful, 1 fp64.
+// bgr: n x 3 fp32 in the network's channel order (B,G,R). mode 0 ref-faithful, 1 fp64,
+// 2 = the batched GEMM statement of mode 0 (nif_fast.cpp; the timed CPU baseline, never a checker).
 int orc_nif_forward(const Nif* nif, int n, const float* u, const float* v, int mode, float* bgr) {
   if (nif->numLayers < 1 || nif->layers[nif->numLayers - 1].out < 3) return -1;
+  if (mode == 2) return nifForwardFast(nif, n, u, v, bgr);
   const int E = nif->embeddingDim;
   const int nFeat = 4 * E;
   const std::vector<LayerF32> ls = unpack(*nif);

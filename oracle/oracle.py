@@ -144,6 +144,13 @@ class Oracle:
     def num_threads(self) -> int:
         return int(self.lib.orc_num_threads())
 
+    def use_all_host_threads(self) -> int:
+        """Lift an inherited OMP_NUM_THREADS=1 (torch.distributed.run sets it): the CPU arm runs on every
+        host thread this process may use. Returns the thread count now in force."""
+        n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        self.lib.orc_set_num_threads(int(n))
+        return self.num_threads()
+
     def camera_rays(self, items: np.ndarray, noise_bits: np.ndarray, s: Settings) -> np.ndarray:
         n = len(items)
         items = np.ascontiguousarray(items, dtype=TRACE_RECORD)

@@ -416,6 +416,9 @@ void orc_trace_philox(int n, const TraceRec* items, std::uint32_t sample, const 
 }
 
 int orc_num_threads() { return omp_get_max_threads(); }
+// bench.py under torch.distributed.run inherits OMP_NUM_THREADS=1; the CPU arm asks for every host thread.
+void orc_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int orc_num_procs() { return omp_get_num_procs(); }
 
 // Raw generator access so tests can compare the CUDA Philox / noise code word for word.
 void orc_philox(std::uint32_t c0, std::uint32_t c1, std::uint32_t c2, std::uint32_t c3, std::uint32_t k0, std::uint32_t k1, std::uint32_t* out4) {

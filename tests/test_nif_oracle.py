@@ -82,3 +82,25 @@ def test_skip_concat_autodetect(O, orc):
 def test_flops_formula(orc, nif_model, oracle_nif):
     # NifModel.cpp:122-134; nominal topology -> 1 089 283
     assert orc.nif_flops_per_eval(oracle_nif) == nif_model.flops_per_eval() == 1089283
+
+
+def test_fast_cpu_nif_matches_the_scalar_restatement(orc, oracle_nif):
+    """oracle/nif_fast.cpp (mode 2: the batched AVX GEMM that bench.py's CPU legs TIME) states the same network
+    as the scalar restatement (mode 0, the checker): decoded log-radiance within 1e-3 (it is in fact equal on almost
+    every ray: both round every Dense output to binary16's significand; only fp32 summation order / FMA differ),
+    including a ragged last batch and a batch of one."""
+    rng = np.random.default_rng(11)
+    for n in (1, 7, 384, 5000):
+        u = rng.random(n).astype(np.float32); v = rng.random(n).astype(np.float32)
+        a = orc.nif_forward(oracle_nif, u, v, 0)
+        b = orc.nif_forward(oracle_nif, u, v, 2)
+        assert np.all(np.isfinite(b))
+        assert np.abs(np.log(a) - np.log(b)).max() < 1e-3
+    assert (a == b).mean() > 0.99
+
+
+def test_cpu_arm_uses_all_host_threads_under_torchrun_env(orc):
+    """torch.distributed.run exports OMP_NUM_THREADS=1; the CPU arm lifts it."""
+    import os
+    n = orc.use_all_host_threads()
+    assert n == len(os.sched_getaffinity(0))
