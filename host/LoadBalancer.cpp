@@ -112,3 +112,12 @@ void LoadBalancer::clearActiveAccumulators() {
     t.sampleCount = 0;
   }
 }
+
+std::uint64_t LoadBalancer::activeOrderDigest() {
+  std::uint64_t h = 1469598103934665603ull;
+  for (const auto& t : work.active()) {
+    h = (h ^ t.u) * 1099511628211ull;
+    h = (h ^ t.v) * 1099511628211ull;
+  }
+  return h;
+}

@@ -55,6 +55,8 @@ struct LoadBalancer {
   /// Zero the accumulators of the inactive list, return the path-length sum ("rays", :198-214).
   std::size_t clearInactiveAccumulators();
   void clearActiveAccumulators();
+  /// FNV-1a over the (u, v) sequence of the active list: which pixel sits in which slot of which job.
+  std::uint64_t activeOrderDigest();
 
 private:
   WorkList work;

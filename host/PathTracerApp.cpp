@@ -255,17 +255,20 @@ RenderSummary PathTracerApp::execute() {
     // Do the simple thing and restart the entire render if any state changed (:651-675):
     if (uiServer && !uiServer->connected()) {
       logging::warn("Remote UI connection lost: rendering continues head-less.");
+      hostProcessing.waitForCompletion();        // the async task of the last step may still be talking to the server
       uiServer.reset();
     }
     if (uiServer && uiServer->stateChanged()) {
       state = uiServer->consumeState();
       const auto status = processUserInput(state);
       if (status == InterfaceServer::Status::Stop) {
+        hostProcessing.waitForCompletion();
         uiServer.reset();
         summary.steps = step - 1;
         break;
       }
       if (status == InterfaceServer::Status::Disconnected) {
+        hostProcessing.waitForCompletion();
         uiServer.reset();
       } else if (status == InterfaceServer::Status::Restart) {
         // reset_host_render_state: drain, then clear the film and the work-item accumulators
@@ -295,8 +298,10 @@ RenderSummary PathTracerApp::execute() {
 
     // Run path tracing on the GPUs (setup / path_trace / read_results, :690-694). Results go into the
     // active buffer whilst the async host task processes the last result from the inactive buffer.
-    if (recordStream)
+    if (recordStream) {
+      if (loadBalanceEnabled) logging::debug("Work list order digest at step {}: {}", step, work.activeOrderDigest());
       for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
+    }
     for (auto& g : gpus) check(b200pt_path_trace(g->ctx), *g, "path_trace");     // asynchronous: all GPUs run concurrently
     std::size_t stepRays = 0;
     for (std::size_t g = 0; g < gpus.size(); ++g) {
@@ -318,11 +323,12 @@ RenderSummary PathTracerApp::execute() {
 
     const bool saveNow = (step % saveInterval == 0) || step == steps;
     if (recordStream) {
-      // Swap the worklist buffers; the host thread processes the results in the now inactive list.
+      // Swap the worklist buffers (PathTracerApp.cpp:707-709): the list the previous async task accumulated, re-dealt
+      // and cleared becomes active; the host thread processes the results just read in the now inactive list. Both
+      // lists hold every pixel (LoadBalancer's constructor), so the two alternate and a re-deal of one list takes
+      // effect at the step after next, exactly as in the reference.
       work.getWork().swap();
-      work.getWork().active() = work.getWork().inactive();     // same items, accumulators cleared below for the GPU
-      work.clearActiveAccumulators();
-      hostProcessing.run([&, step, saveNow]() {
+      hostProcessing.run([&, step, saveNow, exposure = state.exposure, gamma = state.gamma]() {
         film.accumulate(work.getWork().inactive());
         if (loadBalanceEnabled && step > 1) work.allocateWorkByPathLength();
         totalRays = work.clearInactiveAccumulators();
@@ -331,7 +337,7 @@ RenderSummary PathTracerApp::execute() {
           // files are written on the final step only.
           if (uiServer) uiServer->startSendingRawImage(film.getHdrImage(), imageWidth, imageHeight, step, step == steps);
           if (!uiServer || step == steps) {
-            film.saveImages(fileName, step, state.exposure, state.gamma);
+            film.saveImages(fileName, step, exposure, gamma);
             logging::info("Saved images at step {}", step);
           }
         }
@@ -344,8 +350,8 @@ RenderSummary PathTracerApp::execute() {
         gatherDeviceFilm(film);
         if (uiServer) uiServer->startSendingRawImage(film.getHdrImage(), imageWidth, imageHeight, step, step == steps);
         if (!uiServer || step == steps)
-          hostProcessing.run([&, step]() {
-            film.saveImages(fileName, step, state.exposure, state.gamma);
+          hostProcessing.run([&, step, exposure = state.exposure, gamma = state.gamma]() {
+            film.saveImages(fileName, step, exposure, gamma);
             logging::info("Saved images at step {}", step);
           });
       }

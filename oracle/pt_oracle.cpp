@@ -266,9 +266,11 @@ static void escapedUv(V3 d, float azimuth, float& u, float& v) {
   // `atan2` is called unqualified on floats in the reference (codelets.cpp:334); with
   // glibc/libstdc++ that resolves to the double overload, so phi and the wrap run in double
   // and v is rounded to float once at the end. `auto` keeps whatever the toolchain picks.
-  // Deviation from codelets.cpp:333 shared with the CUDA path: |d.y| can be 1 + 1 ulp after normalisation, for which acosf
-  // (and hence the pixel, for ever) is NaN in the reference; both implementations clamp to the vertical direction.
-  const auto theta = acosf(std::fmin(std::fmax(d.y, -1.f), 1.f));
+  // Reference-exact (codelets.cpp:333): |d.y| can be 1 + 1 ulp after normalisation, for which acosf - and hence the
+  // pixel, for ever - is NaN in the reference, and so it is here. The CUDA path deliberately clamps d.y to [-1, 1]
+  // (pt_device.cuh escapedUv); tests assert that difference (tests/test_gpu_kat.py::test_escaped_uv) instead of
+  // bending the oracle to the product.
+  const auto theta = acosf(d.y);
   auto phi = atan2(d.z, d.x) + azimuth;
   constexpr auto twoPi = 2.f * kPi;
   constexpr auto invPi = 1.f / kPi;

@@ -172,3 +172,30 @@ def test_cli_remote_ui_runs_to_completion_and_saves(cli, nif_model, tmp_path):
     finally:
         if p.poll() is None:
             p.kill()
+
+
+def test_cli_load_balancing_really_redeals(cli, lib_built, nif_model, O, orc, tmp_path):
+    """--enable-load-balancing (LoadBalancer.cpp:141-192, PathTracerApp.cpp:707-735; ADVICE r1: it used to be a no-op).
+    The two work lists alternate: the list uploaded at steps 1-3 is the initial deal (step 1's task does not re-deal,
+    step 2's task re-deals the OTHER list), from step 4 on every upload is a list re-dealt by path length, so its order
+    digest differs from the initial one. The image stays the oracle's (RNG is keyed on the pixel, not the slot)."""
+    import re
+    import cv2
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    import torch
+    gpus = min(2, torch.cuda.device_count())
+    w, h, spp, per_step = 96, 64, 24, 4
+    assets = _assets(tmp_path, nif_model)
+    out = str(tmp_path / "lb.png")
+    r = subprocess.run([cli, "-o", out, "--assets", assets, "-w", str(w), "-h", str(h), "-s", str(spp), "--samples-per-step", str(per_step),
+                        "--save-interval", "6", "--seed", "1", "--enable-load-balancing", "--ipus", str(gpus), "--log-level", "debug"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    digests = dict((int(a), b) for a, b in re.findall(r"Work list order digest at step (\d+): (\d+)", r.stderr))
+    assert sorted(digests) == [1, 2, 3, 4, 5, 6], r.stderr[-3000:]
+    assert digests[1] == digests[2] == digests[3]
+    assert digests[4] != digests[1] and digests[5] != digests[1] and digests[6] != digests[4]
+    assert r.stderr.count("Load balancing started") == 5          # every step but the first
+    exr = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED).astype(np.float64)
+    want = _oracle_film(O, orc, lib_built, nif_model, w, h, spp)
+    assert _rrmse(exr, want) < 0.01

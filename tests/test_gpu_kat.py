@@ -99,6 +99,13 @@ def test_escaped_uv(pt, golden, O):
                      [0.0, 1.0, 0.0, 0.0], [0.0, -1.0, 0.0, 0.0]], np.float32)
     uv = pt.kat(T.KAT_ESCAPED_UV, edge, 2)
     assert np.isfinite(uv).all() and uv[0, 0] == 0.0 and uv[2, 0] == 0.0 and abs(uv[1, 0] - 1.0) < 1e-6 and abs(uv[3, 0] - 1.0) < 1e-6
+    # ... and the oracle stays reference-exact: NaN for the two out-of-domain rows, the GPU's bits for the two in-domain rows
+    erec = np.zeros((4, 1), O.CONTRIB)
+    erec["clr"][:, 0, :] = edge[:, :3]; erec["weight"] = 1.0; erec["type"] = O.C_ESCAPED
+    ou, ov = O.Oracle().escaped_uv(erec, 0.0)
+    assert np.isnan(ou[0]) and np.isnan(ou[1])
+    assert np.array_equal(ou[2:].view(np.uint32), uv[2:, 0].astype(np.float32).view(np.uint32))
+    assert np.array_equal(ov.view(np.uint32), uv[:, 1].astype(np.float32).view(np.uint32))
 
 
 def test_philox_bit_exact(pt, orc):

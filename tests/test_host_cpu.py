@@ -15,14 +15,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HOST = os.path.join(ROOT, "host")
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
-METADATA = {   # the fields of the shipped assets.extra/nif_metadata.txt the loader reads (NifMetaData.cpp:19-64)
-    "embedding_dimension": 12, "embedding_sigma": 2.0,
-    "encode_params": {"eps": 1e-08, "log_tone_map": True, "max": 3.4299468994140625,
-                      "mean": [-2.3514461517333984, -2.2660605907440186, -1.9648972749710083], "transfer_function": "log"},
-    "keras_model": "/x/urban_alley_01_4k_fp16_yuv", "name": "/x/hdris/urban_alley_01_4k.exr",
-    "original_image_shape": [2048, 4096, 3],
-    "train_command": ["train_nif.py", "--fp16", "--layer-count", "6", "--layer-size", "320", "--embedding-dimension", "12"],
-}
+# The shipped metadata of the reference's NIF model, verbatim (nif_models/urban_alley_01_4k_fp16_yuv/assets.extra/
+# nif_metadata.txt; a 1.2 KB data fixture, the weights blob next to it is missing from the snapshot).
+SHIPPED_METADATA = os.path.join(ROOT, "tests", "golden", "nif_metadata.txt")
+METADATA = json.load(open(SHIPPED_METADATA))
 
 
 @pytest.fixture(scope="session")
@@ -237,6 +233,28 @@ def test_metadata_and_nif_bin_loader(host, tmp_path):
     for got, raw in zip(mean, METADATA["encode_params"]["mean"]):
         assert np.float32(got) == np.float32(np.float32(raw) - np.float32(1e-8))
     assert np.float32(float(f["max"])) == np.float32(3.4299468994140625)
+
+
+def test_shipped_metadata_file_parses_like_nifmetadata(host, tmp_path):
+    """NifMetaData.cpp:11-71 on the reference's own nif_metadata.txt (byte-for-byte copy under tests/golden/), through the C++
+    loader (host/NifAssets.cpp) and the Python mirror: embedding 12, eps folded into the mean (:48-53), max, the hidden
+    size scraped from `--layer-size` in train_command (:55-64), name and image shape."""
+    import shutil
+    from ipu_path_trace_b200.nif import NifMetaData
+    d = tmp_path / "assets.extra"
+    d.mkdir()
+    shutil.copy(SHIPPED_METADATA, d / "nif_metadata.txt")
+    want_mean = [np.float32(np.float32(m) - np.float32(1e-8)) for m in (-2.3514461517333984, -2.2660605907440186, -1.9648972749710083)]
+    md = NifMetaData.load(str(d / "nif_metadata.txt"))
+    assert md.embedding_dimension == 12 and md.hidden_size == 320 and md.log_tone_map is True
+    assert md.name == "/home/ubuntu/workspace/hdris/urban_alley_01_4k.exr" and md.image_shape == (2048, 4096, 3)
+    assert np.float32(md.max) == np.float32(3.4299469) and np.float32(md.eps) == np.float32(1e-8)
+    assert [np.float32(m) for m in md.mean] == want_mean
+    f, shapes, _ = _load(host, str(d), synthetic=1)        # no weights next to it: synthetic ones in the topology the metadata names
+    assert f["E"] == "12" and f["hidden"] == "320" and f["log"] == "1"
+    assert np.float32(float(f["max"])) == np.float32(3.4299469)
+    assert [np.float32(float(x)) for x in f["mean"].split(",")] == want_mean
+    assert shapes.startswith("48x320") and shapes.count("|") == 7
 
 
 def test_asset_errors(host, tmp_path):
@@ -467,3 +485,70 @@ def test_cornell_cli_options_and_no_cpu_path(tmp_path):
         assert not os.path.exists(out) and not os.path.exists(out + ".exr")
         opts = dict(l.split(" ", 1) for l in open(out + ".command_line_options").read().splitlines())
         assert opts["width"] == "16" and opts["samples"] == "2" and opts["seed"] == "1"
+
+
+def test_ui_protocol_with_the_references_own_client(host):
+    """The same session as test_ui_protocol_progress_image_restart_and_stop, but the peer is the REFERENCE's packetcomms
+    (PacketDemuxer / PacketMuxer / TcpSocket) + cereal compiled unmodified into oracle/_ref/libref_uiclient.so, with the packet
+    table and the HdrHeader / HdrPacket / SampleRates serialisers of src/InterfaceServer.hpp:21-83: host/InterfaceServer.hpp
+    and host/PacketComms.hpp interoperate with the reference's implementation of the wire format, in both directions
+    (Hello handshake PacketDemuxer.cpp:110,230-250; framing PacketMuxer.cpp:114-138)."""
+    import threading
+    import ui_ref_client as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libref_uiclient.so not built here (needs /root/reference)")
+    from ui_client import PACKETS
+    port, res = _free_port(), {}
+    t = threading.Thread(target=_ui_session, args=(host, port, res), kwargs=dict(steps=100000, save=3))
+    t.start()
+    c = R.RefUiClient(port)
+    assert c.packet_types() == PACKETS                      # the hand-copied table equals the reference's
+    assert c.wait(lambda c: c._counts()[2] >= 1 and c._counts()[0] >= 3)
+    assert c.ok()                                           # the reference's demuxer accepted our Hello
+    img = c.image(0)
+    assert img.shape == (7, 12, 3)
+    np.testing.assert_array_equal(img, np.broadcast_to(np.float32([8, 0, 1]), img.shape))
+    assert c.rates[0] == (1000.0, 2000.0)
+    assert abs(c.progress[1] - 2 / 100000) < 1e-9
+    c.send_float("exposure", 1.5)
+    c.send_float("gamma", 1.8)
+    n = len(c.progress)
+    assert c.wait(lambda c: c._counts()[0] >= n + 3)
+    assert c.progress[-1] > c.progress[n - 1]
+    c.send_float("fov", 180.0)
+    c.send_float("env_rotation", 45.0)
+    c.send_u32("interactive_samples", 3)
+    c.send_string("load_nif", "/some/where/assets.extra")
+    assert c.wait(lambda c: c._counts()[2] and np.allclose(c.image(-1)[0, 0], [3, 45, np.float32(np.pi)]))
+    p = c.progress
+    assert 1 <= sum(1 for a, b in zip(p, p[1:]) if b < a) <= 4
+    c.send_bool("stop")
+    t.join(30)
+    assert not t.is_alive() and res["rc"] == 0, res
+    o = res["out"]
+    assert o["stopped"] == "1" and 1 <= int(o["restarts"]) <= 4
+    assert float(o["exposure"]) == 1.5 and abs(float(o["gamma"]) - 1.8) < 1e-6
+    assert abs(float(o["fov"]) - np.pi) < 1e-6 and float(o["rot"]) == 45.0 and o["isamples"] == "3"
+    assert o["nif"] == "/some/where/assets.extra"
+    assert c.wait_closed(10)                                # the reference's demuxer sees our GoodBye / hang-up
+    c.close()
+
+
+def test_ui_heartbeat_keeps_the_references_client_alive(host):
+    """An idle link: the reference's demuxer drops a peer that stays silent (it expects HeartBeat control packets,
+    PacketMuxer.cpp:62-77); two 1.4 s steps with nothing to say must leave its ok() true until the server leaves."""
+    import threading
+    import ui_ref_client as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libref_uiclient.so not built here (needs /root/reference)")
+    port, res = _free_port(), {}
+    t = threading.Thread(target=_ui_session, args=(host, port, res), kwargs=dict(steps=2, save=100, step_ms=1400))
+    t.start()
+    c = R.RefUiClient(port)
+    import time
+    time.sleep(1.2)
+    assert c.ok()
+    t.join(30)
+    assert res["rc"] == 0 and res["out"]["steps"] == "2"
+    assert c.wait(lambda c: c._counts()[2] >= 1, timeout=10)   # the final image is always delivered
+    c.close()
