@@ -29,7 +29,21 @@ namespace b2 {
 
 constexpr int kTcRows = 128;
 constexpr int kEncodeWarps = 4;
-constexpr int kEpiWarps = 8;
+// Epilogue warps: 8 (two per TMEM lane quadrant, 80 columns of a half-job each) or 16 (four per quadrant, 40 columns
+// each). The hand-over of a half-job's activations to the next layer's first MMAs has to fit into the ~800 cycles of the
+// layer's last weight chunk; with 8 warps it takes ~800-1000 cycles and the tensor pipe waits ~570 cycles per layer.
+#ifndef B200PT_EPI_WARPS
+#define B200PT_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = B200PT_EPI_WARPS;
+static_assert(kEpiWarps == 8 || kEpiWarps == 16, "two or four epilogue warps per TMEM lane quadrant");
+constexpr int kEpiColParts = kEpiWarps / 4;      // column parts of a half-job
+constexpr int kEpiGroup = kEpiWarps == 8 ? 16 : 8;   // accumulator columns per tcgen05.ld
+#ifndef B200PT_EPI_FRONT
+#define B200PT_EPI_FRONT (B200PT_EPI_WARPS == 16)
+#endif
+constexpr bool kEpiFrontLoad = B200PT_EPI_FRONT != 0;   // request every accumulator column of a job before converting
+constexpr int kOutWarps = 4;                     // the warps of column part 0 also run the output job
 constexpr int kTcThreads = 32 * (3 + kEncodeWarps + kEpiWarps);
 constexpr int kSecondIssuerWarp = 2 + kEncodeWarps + kEpiWarps;   // single-CTA MMA variants issue from two warps in turn
 constexpr int kFirstEncodeWarp = 2;
@@ -157,6 +171,17 @@ __device__ __forceinline__ void tcLoad16(uint32_t taddr, uint32_t (&v)[16]) {
         "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
       : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tcLoad8(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tcStore4(uint32_t taddr, const uint32_t (&v)[4]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+}
+__device__ __forceinline__ void tcLoadN(uint32_t taddr, uint32_t (&v)[16]) { tcLoad16(taddr, v); }
+__device__ __forceinline__ void tcLoadN(uint32_t taddr, uint32_t (&v)[8]) { tcLoad8(taddr, v); }
+__device__ __forceinline__ void tcStoreN(uint32_t taddr, const uint32_t (&v)[8]) { tcStore8(taddr, v); }
+__device__ __forceinline__ void tcStoreN(uint32_t taddr, const uint32_t (&v)[4]) { tcStore4(taddr, v); }
 __device__ __forceinline__ bool electOne() {
   uint32_t pred;
   asm volatile("{ .reg .pred p; elect.sync _|p, 0xffffffff; selp.u32 %0, 1, 0, p; }" : "=r"(pred));
@@ -291,7 +316,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     for (int b = 0; b < (int)kSlots; ++b) { mbarInit(bar(BAR_ACC_FULL + b), 1); mbarInit(bar(BAR_ACC_EMPTY + b), CG * kEpiWarps); }
     *reinterpret_cast<volatile uint32_t*>(smem + L.bars + 8 * SLOT_TURN) = 0u;
     mbarInit(bar(BAR_OUT_FULL), 1);
-    mbarInit(bar(BAR_OUT_EMPTY), CG * kEpiWarps / 2);
+    mbarInit(bar(BAR_OUT_EMPTY), CG * kOutWarps);
     fenceBarrierInit();
   }
   if (warp == 1) {
@@ -521,10 +546,10 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
     // ================= epilogue =================
     const uint32_t ew = warp - kFirstEpiWarp;
     const uint32_t quad = warp & 3u;                      // TMEM lane quadrant this warp may read
-    const uint32_t colHalf = ew >> 2;                     // which half of a job's NH columns
+    const uint32_t colHalf = (warp - (uint32_t)kFirstEpiWarp) >> 2;   // which part of a job's NH columns
     const uint32_t r = quad * 32u + lane;                 // tile row == TMEM lane
-    const uint32_t colsMine = (uint32_t)NH / 2u;          // multiple of 16, <= 80
-    const uint32_t groups = colsMine / 16u;               // <= 5
+    const uint32_t colsMine = (uint32_t)NH / (uint32_t)kEpiColParts;   // multiple of kEpiGroup
+    const uint32_t groups = colsMine / (uint32_t)kEpiGroup;            // <= 5
     const uint32_t laneBase = tmemBase + ((quad * 32u) << 16);
     const __half2 one2 = __float2half2_rn(1.f);
     uint32_t it = 0;
@@ -541,33 +566,55 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           tcFenceAfter();
           const uint32_t tBase = laneBase + accCol0 + buf * (uint32_t)NH + colHalf * colsMine;
           const uint32_t colBase = h * (uint32_t)NH + colHalf * colsMine;      // output-neuron index of my first column
-          // software pipeline: the load of group g+1 is in flight while group g is converted and stored
-          uint32_t v[2][16];
-          tcLoad16(tBase, v[0]);
-#pragma unroll
-          for (uint32_t g = 0; g < 5; ++g) {
-            if (g < groups) {
-              tcWaitLoad();
-              if (g + 1 < groups) tcLoad16(tBase + (g + 1) * 16u, v[(g + 1) & 1]);
-              const uint32_t c0 = colBase + g * 16u;
+          constexpr int GW = kEpiGroup, GP = kEpiGroup / 2;     // accumulator columns / packed binary16 pairs per group
+          // one group: round to binary16, + bias, ReLU, write the next layer's A operand
+          auto emit = [&](uint32_t g, const uint32_t (&acc)[GW]) {
+            const uint32_t c0 = colBase + g * (uint32_t)GW;
+            uint32_t bw[GP];
+            {
               const uint4 b0 = *reinterpret_cast<const uint4*>(biasRow + c0 * 2u);
-              const uint4 b1 = *reinterpret_cast<const uint4*>(biasRow + c0 * 2u + 16u);
-              const uint32_t bw[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-              uint32_t packed[8];
-#pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                __half2 hv = __floats2half2_rn(__uint_as_float(v[g & 1][2 * q]), __uint_as_float(v[g & 1][2 * q + 1]));
-                // x * 1 + bias is one rounding, like the add; the relu variant clamps in the same instruction
-                const __half2 bq = *reinterpret_cast<const __half2*>(&bw[q]);
-                hv = relu ? __hfma2_relu(hv, one2, bq) : __hadd2(hv, bq);
-                packed[q] = *reinterpret_cast<uint32_t*>(&hv);
+              bw[0] = b0.x; bw[1] = b0.y; bw[2] = b0.z; bw[3] = b0.w;
+              if (GP == 8) {
+                const uint4 b1 = *reinterpret_cast<const uint4*>(biasRow + c0 * 2u + 16u);
+                bw[GP - 4] = b1.x; bw[GP - 3] = b1.y; bw[GP - 2] = b1.z; bw[GP - 1] = b1.w;
               }
-              if (TS) {
-                tcStore8(laneBase + c0 / 2u, packed);            // neuron c -> TMEM column c / 2 (binary16 pairs)
-              } else {
-                unsigned char* dst = smem + L.act + (c0 / 8u) * 2048u + r * 16u;
-                *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-                *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            }
+            uint32_t packed[GP];
+#pragma unroll
+            for (int q = 0; q < GP; ++q) {
+              __half2 hv = __floats2half2_rn(__uint_as_float(acc[2 * q]), __uint_as_float(acc[2 * q + 1]));
+              // x * 1 + bias is one rounding, like the add; the relu variant clamps in the same instruction
+              const __half2 bq = *reinterpret_cast<const __half2*>(&bw[q]);
+              hv = relu ? __hfma2_relu(hv, one2, bq) : __hadd2(hv, bq);
+              packed[q] = *reinterpret_cast<uint32_t*>(&hv);
+            }
+            if (TS) {
+              tcStoreN(laneBase + c0 / 2u, packed);            // neuron c -> TMEM column c / 2 (binary16 pairs)
+            } else {
+              unsigned char* dst = smem + L.act + (c0 / 8u) * 2048u + r * 16u;
+              *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+              if (GP == 8) *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(packed[GP - 4], packed[GP - 3], packed[GP - 2], packed[GP - 1]);
+            }
+          };
+          if (kEpiFrontLoad) {
+            // all of this warp's accumulator columns are requested at once: one TMEM round trip per job instead of
+            // one per group (the chain of five dependent round trips is what made a job ~720 cycles long)
+            uint32_t v[5][GW];
+#pragma unroll
+            for (uint32_t g = 0; g < 5; ++g) if (g < groups) tcLoadN(tBase + g * (uint32_t)GW, v[g]);
+            tcWaitLoad();
+#pragma unroll
+            for (uint32_t g = 0; g < 5; ++g) if (g < groups) emit(g, v[g]);
+          } else {
+            // software pipeline: the load of group g+1 is in flight while group g is converted and stored
+            uint32_t v[2][GW];
+            tcLoadN(tBase, v[0]);
+#pragma unroll
+            for (uint32_t g = 0; g < 5; ++g) {
+              if (g < groups) {
+                tcWaitLoad();
+                if (g + 1 < groups) tcLoadN(tBase + (g + 1) * (uint32_t)GW, v[(g + 1) & 1]);
+                emit(g, v[g & 1]);
               }
             }
           }

@@ -1,5 +1,5 @@
 import os, sys; sys.path.insert(0, '.')
-os.environ["B200PT_LIB"] = os.path.abspath("ipu_path_trace_b200/libb200pt_prof.so")
+os.environ.setdefault("B200PT_LIB", os.path.abspath("ipu_path_trace_b200/libb200pt_prof.so"))
 import ctypes as C, numpy as np, torch
 import ipu_path_trace_b200 as pt
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 20
