@@ -225,11 +225,17 @@ def run_ours(args) -> None:
         tracer.film_accumulate()
         tracer.sync()
 
-    out_records = np.zeros(len(worklist), dtype=pt.TRACE_RECORD)
+    # e2e: the reference-facing programs with HOST buffers every step, laid out like the reference's render loop
+    # (PathTracerApp.cpp:690-709): page-locked work list and result buffers (b200pt_host_alloc), and the NEXT step's work
+    # list staged with setup_next while this step's path_trace runs (the reference's double-buffered work list).
+    pin_in = pt.PinnedRecords(len(worklist))
+    pin_out = pt.PinnedRecords(len(worklist))
+    pin_in.array[:] = worklist
+    out_records = pin_out.array
 
     def step_e2e():
-        tracer.setup(worklist)                    # H->D TraceRecords ("setup" program)
-        tracer.path_trace(sync=False)             # "path_trace"
+        tracer.path_trace(sync=False)             # "path_trace" (uses the list staged by the previous step's setup_next)
+        tracer.setup_next(pin_in.array)           # H->D TraceRecords of the next step ("setup"), overlapped with the trace
         return tracer.read_results(out_records)   # D->H TraceRecords + counters ("read_results")
 
     def gather_film():
@@ -262,6 +268,7 @@ def run_ours(args) -> None:
         nif_ms += c.nif_ms; trace_ms += c.trace_ms; dev_ms += c.total_ms
         escaped += c.escaped; paths += c.paths; launches += c.kernel_launches + 1
     # ---- timed: end to end with host buffers ----
+    tracer.setup(pin_in.array)
     for _ in range(min(2, args.warmup)):
         step_e2e()
     e2e_total = 0.0
@@ -322,6 +329,7 @@ def run_ours(args) -> None:
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
         print(json.dumps(line), flush=True)
     tracer.close()
+    pin_in.close(); pin_out.close()
     if dist is not None:
         dist.destroy_process_group()
 

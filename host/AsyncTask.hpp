@@ -9,6 +9,8 @@
 #include <stdexcept>
 #include <thread>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "logging.hpp"
 
 class AsyncTask {
@@ -25,17 +27,21 @@ public:
     }
     asyncFunc = std::move(f);
     failure = nullptr;
+    nvtxRangePushA("thread_launch");      // the reference's tracepoints (src/AsyncTask.hpp:40,49)
+    running = true;                       // set here, not in the thread: isRunning() is true as soon as run() returns
     job.reset(new std::thread([this]() {
-      running = true;
       try { asyncFunc(); } catch (...) { failure = std::current_exception(); }
       running = false;
     }));
+    nvtxRangePop();
   }
 
   /// Joins the job; an exception thrown inside it resurfaces here, on the render thread.
   void waitForCompletion() {
     if (job != nullptr) {
+      nvtxRangePushA("thread_join");
       job->join();
+      nvtxRangePop();
       job.reset();
       if (failure) { auto f = failure; failure = nullptr; std::rethrow_exception(f); }
     }

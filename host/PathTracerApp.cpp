@@ -3,13 +3,25 @@
 #include <cuda_runtime.h>
 #include <nccl.h>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include <chrono>
 #include <cmath>
 #include <sstream>
 #include <stdexcept>
+#include <thread>
 
 #include "AsyncTask.hpp"
 #include "logging.hpp"
+
+namespace {
+// NVTX ranges carrying the names of the reference's PVTI tracepoints (PathTracerApp.cpp:313-780), so that an nsys
+// timeline of this host reads like a PopVision trace of the reference. No-ops unless a tool is attached.
+struct Trace {
+  explicit Trace(const char* name) { nvtxRangePushA(name); }
+  ~Trace() { nvtxRangePop(); }
+};
+} // namespace
 
 std::size_t roundSamplesPerPixel(std::size_t samplesPerPixel, std::size_t samplesPerStep) {
   if (samplesPerPixel % samplesPerStep) {
@@ -70,7 +82,7 @@ bool PathTracerApp::loadNifModels(const std::string& assetPath) {
   return true;
 }
 
-void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, std::size_t itemsPerGpu) {
+std::vector<int> PathTracerApp::deviceList() const {
   const std::size_t numGpus = args->u64("ipus");
   std::vector<int> devices;
   if (args->given("devices")) {
@@ -81,6 +93,12 @@ void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, st
   } else {
     for (std::size_t g = 0; g < numGpus; ++g) devices.push_back((int)g);
   }
+  return devices;
+}
+
+void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, std::size_t itemsPerGpu) {
+  const std::size_t numGpus = args->u64("ipus");
+  const std::vector<int> devices = deviceList();
   const std::string aaName = args->str("aa-noise-type");
   int aaType;
   if (aaName == "normal") aaType = B200PT_AA_NORMAL;
@@ -94,42 +112,67 @@ void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, st
   if (args->given("max-nif-batch-size") && args->u64("max-nif-batch-size") > 0)
     samplesPerLaunch = (std::uint32_t)std::max<std::uint64_t>(1, args->u64("max-nif-batch-size") / std::max<std::size_t>(1, itemsPerGpu));
 
+  // One thread per GPU: context creation (CUDA context, 0.3-1 GB of device buffers) and the NIF upload (packing the
+  // weight stream, 3 MB feature table) take ~1 s each and used to run one GPU after the other.
+  gpus.resize(numGpus);
+  std::vector<std::string> errors(numGpus);
+  std::vector<std::thread> workers;
+  const b200pt_nif_desc desc = nif->descriptor();
   for (std::size_t g = 0; g < numGpus; ++g) {
-    std::unique_ptr<Gpu> gpu(new Gpu());
-    gpu->device = devices[g];
-    b200pt_config cfg{};
-    cfg.struct_size = sizeof(cfg);
-    cfg.device = devices[g];
-    cfg.width = width; cfg.height = height;
-    cfg.max_path_length = args->u32("max-path-length");
-    cfg.roulette_depth = args->u32("roulette-depth");
-    cfg.stop_prob = args->f32("stop-prob");
-    cfg.refractive_index = args->f32("refractive-index");
-    cfg.aa_noise_type = aaType;
-    cfg.max_worklist = (std::uint32_t)itemsPerGpu;
-    cfg.samples_per_launch = samplesPerLaunch;
-    cfg.nif_impl = B200PT_NIF_AUTO;
-    const int rc = b200pt_create(&cfg, &gpu->ctx);
-    if (rc != B200PT_OK) {
+    workers.emplace_back([&, g]() {
+      Trace t("create_context");
+      std::unique_ptr<Gpu> gpu(new Gpu());
+      gpu->device = devices[g];
+      b200pt_config cfg{};
+      cfg.struct_size = sizeof(cfg);
+      cfg.device = devices[g];
+      cfg.width = width; cfg.height = height;
+      cfg.max_path_length = args->u32("max-path-length");
+      cfg.roulette_depth = args->u32("roulette-depth");
+      cfg.stop_prob = args->f32("stop-prob");
+      cfg.refractive_index = args->f32("refractive-index");
+      cfg.aa_noise_type = aaType;
+      cfg.max_worklist = (std::uint32_t)itemsPerGpu;
+      cfg.samples_per_launch = samplesPerLaunch;
+      cfg.nif_impl = B200PT_NIF_AUTO;
       std::stringstream ss;
-      ss << "Could not create a render context on GPU " << devices[g] << " (" << rc << "): " << b200pt_last_error(nullptr);
-      throw std::runtime_error(ss.str());
-    }
-    gpus.push_back(std::move(gpu));
+      int rc = b200pt_create(&cfg, &gpu->ctx);
+      if (rc != B200PT_OK) {
+        ss << "Could not create a render context on GPU " << devices[g] << " (" << rc << "): " << b200pt_last_error(nullptr);
+        errors[g] = ss.str();
+        return;
+      }
+      rc = b200pt_upload_nif(gpu->ctx, &desc);      // init_nif_weights (PathTracerApp.cpp:610)
+      if (rc != B200PT_OK) {
+        ss << "init_nif_weights failed on GPU " << devices[g] << " (" << rc << "): " << b200pt_last_error(gpu->ctx);
+        errors[g] = ss.str();
+        return;
+      }
+      gpus[g] = std::move(gpu);
+    });
   }
+  for (auto& w : workers) w.join();
+  for (auto& e : errors) if (!e.empty()) { gpus.clear(); throw std::runtime_error(e); }
   logging::info("Created {} GPU context(s): {}", gpus.size(), b200pt_version());
 }
 
 // Communicators and staging buffers of the film gather; created before the render starts so that the first save
 // interval does not pay for ncclCommInitAll.
+// ncclCommInitAll takes seconds for 8 GPUs; it needs only the device ordinals, so execute() runs it on its own thread
+// beside context creation and the NIF upload.
+void PathTracerApp::initFilmGatherComms() {
+  Trace t("nccl_comm_init");
+  std::unique_ptr<FilmGather> fg(new FilmGather());
+  std::vector<int> devs = deviceList();
+  fg->comms.assign(devs.size(), nullptr);
+  const ncclResult_t r = ncclCommInitAll(fg->comms.data(), (int)devs.size(), devs.data());
+  if (r != ncclSuccess) throw std::runtime_error(std::string("ncclCommInitAll: ") + ncclGetErrorString(r));
+  gather = std::move(fg);
+}
+
 void PathTracerApp::initFilmGather(std::size_t n) {
   auto cuda = [](cudaError_t e, const char* what) { if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e)); };
-  auto nccl = [](ncclResult_t r, const char* what) { if (r != ncclSuccess) throw std::runtime_error(std::string(what) + ": " + ncclGetErrorString(r)); };
-  gather.reset(new FilmGather());
-  std::vector<int> devs;
-  for (auto& g : gpus) devs.push_back(g->device);
-  gather->comms.assign(gpus.size(), nullptr);
-  nccl(ncclCommInitAll(gather->comms.data(), (int)gpus.size(), devs.data()), "ncclCommInitAll");
+  if (!gather) initFilmGatherComms();
   for (auto& g : gpus) {
     cuda(cudaSetDevice(g->device), "cudaSetDevice");
     cuda(cudaMalloc(&g->staging, n * sizeof(float)), "cudaMalloc");
@@ -151,7 +194,7 @@ void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
   }
   auto cuda = [](cudaError_t e, const char* what) { if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e)); };
   auto nccl = [](ncclResult_t r, const char* what) { if (r != ncclSuccess) throw std::runtime_error(std::string(what) + ": " + ncclGetErrorString(r)); };
-  if (!gather) initFilmGather(n);
+  if (!gather || !gpus[0]->reduced) initFilmGather(n);
   for (auto& g : gpus) check(b200pt_film_read_device(g->ctx, g->staging, 1.f), *g, "film_read_device");   // synchronises the context
   nccl(ncclGroupStart(), "ncclGroupStart");
   for (std::size_t i = 0; i < gpus.size(); ++i)
@@ -210,16 +253,28 @@ RenderSummary PathTracerApp::execute() {
 
   auto startTime = std::chrono::steady_clock::now();
 
+  nvtxRangePushA("initialisation");
+  // The film-gather communicators are built beside everything else (they only need the device ordinals).
+  std::thread ncclThread;
+  std::exception_ptr ncclError;
+  if (!recordStream && args->u64("ipus") > 1)
+    ncclThread = std::thread([&]() { try { initFilmGatherComms(); } catch (...) { ncclError = std::current_exception(); } });
+  struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } ncclJoiner{ncclThread};
+
   // Build the tracing jobs (initialiseState, PathTracerApp.cpp:484-497): pixel tiles dealt to GPUs.
+  nvtxRangePushA("create_path_tracing_jobs");
   auto jobs = createTracingJobs(imageWidth, imageHeight, args->u64("ipus"));
+  nvtxRangePop();
   logging::info("Created worklists for {} GPUs ({} work items each)", jobs.size(), jobs.front().size());
   LoadBalancer work(jobs);
-  AccumulatedImage film(imageWidth, imageHeight);
+  // Two host films: the one being encoded by the save task and the one the next gather writes into.
+  AccumulatedImage films[2] = {AccumulatedImage(imageWidth, imageHeight), AccumulatedImage(imageWidth, imageHeight)};
+  AccumulatedImage& film = films[0];
+  std::size_t saveBuffer = 0, skippedSaves = 0;
+  // Contexts and init_nif_weights (:610), one thread per GPU.
   createContexts(imageWidth, imageHeight, work.jobSize());
-
-  // init_nif_weights, init_render_settings (:610-611)
-  b200pt_nif_desc desc = nif->descriptor();
-  for (auto& g : gpus) check(b200pt_upload_nif(g->ctx, &desc), *g, "init_nif_weights");
+  if (ncclThread.joinable()) ncclThread.join();
+  if (ncclError) std::rethrow_exception(ncclError);
 
   // Setup remote user interface (:618-633). Unlike the reference the state a client has not touched
   // yet starts from the command line, with or without a client.
@@ -241,6 +296,9 @@ RenderSummary PathTracerApp::execute() {
   if (!recordStream && gpus.size() > 1) initFilmGather((std::size_t)imageWidth * imageHeight * 3);
   if (!recordStream)
     for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
+  nvtxRangePop();      // initialisation
+  logging::info("Initialisation took {} seconds", std::chrono::duration<double>(std::chrono::steady_clock::now() - startTime).count());
+  nvtxRangePushA("rendering");
 
   AsyncTask hostProcessing;
   RenderSummary summary;
@@ -298,6 +356,7 @@ RenderSummary PathTracerApp::execute() {
 
     // Run path tracing on the GPUs (setup / path_trace / read_results, :690-694). Results go into the
     // active buffer whilst the async host task processes the last result from the inactive buffer.
+    nvtxRangePushA("ipu_render");
     if (recordStream) {
       if (loadBalanceEnabled) logging::debug("Work list order digest at step {}: {}", step, work.activeOrderDigest());
       for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
@@ -317,9 +376,10 @@ RenderSummary PathTracerApp::execute() {
       logging::debug("GPU {}: path-trace {} ms, NIF {} ms, total {} ms", gpus[g]->device, ctr.trace_ms, ctr.nif_ms, ctr.total_ms);
     }
 
+    nvtxRangePop();      // ipu_render
     // Wait for completion of previous async task before starting the next (:702-706). With the device film
     // the host thread only ever holds a gathered copy, so the wait moves to the next gather.
-    if (recordStream) hostProcessing.waitForCompletion();
+    if (recordStream) { Trace t("wait_for_host"); hostProcessing.waitForCompletion(); }
 
     const bool saveNow = (step % saveInterval == 0) || step == steps;
     if (recordStream) {
@@ -329,14 +389,16 @@ RenderSummary PathTracerApp::execute() {
       // effect at the step after next, exactly as in the reference.
       work.getWork().swap();
       hostProcessing.run([&, step, saveNow, exposure = state.exposure, gamma = state.gamma]() {
-        film.accumulate(work.getWork().inactive());
-        if (loadBalanceEnabled && step > 1) work.allocateWorkByPathLength();
-        totalRays = work.clearInactiveAccumulators();
+        Trace t("async_work");
+        { Trace t1("accumulate_framebuffers"); film.accumulate(work.getWork().inactive()); }
+        if (loadBalanceEnabled && step > 1) { Trace t2("run_load_balancing"); work.allocateWorkByPathLength(); }
+        { Trace t3("clear_accumulators"); totalRays = work.clearInactiveAccumulators(); }
         if (saveNow) {
           // With a UI server the full uncompressed image is transmitted at the save interval (:748-759);
           // files are written on the final step only.
           if (uiServer) uiServer->startSendingRawImage(film.getHdrImage(), imageWidth, imageHeight, step, step == steps);
           if (!uiServer || step == steps) {
+            Trace t4("save_images");
             film.saveImages(fileName, step, exposure, gamma);
             logging::info("Saved images at step {}", step);
           }
@@ -345,15 +407,27 @@ RenderSummary PathTracerApp::execute() {
     } else {
       totalRays = stepRays;
       if (saveNow) {
-        // one gather per save interval; encoding and writing the files overlaps the next steps
-        hostProcessing.waitForCompletion();
-        gatherDeviceFilm(film);
-        if (uiServer) uiServer->startSendingRawImage(film.getHdrImage(), imageWidth, imageHeight, step, step == steps);
-        if (!uiServer || step == steps)
-          hostProcessing.run([&, step, exposure = state.exposure, gamma = state.gamma]() {
-            film.saveImages(fileName, step, exposure, gamma);
-            logging::info("Saved images at step {}", step);
-          });
+        // One gather per save interval; encoding and writing the files overlaps the next steps. A save interval never
+        // stalls a step: if the previous encode is still running the interval is skipped (as the reference drops a
+        // raw-image request while a transfer is in progress, InterfaceServer.hpp:282-286) - except on the final step.
+        const bool last = step == steps;
+        if (hostProcessing.isRunning() && !last) {
+          skippedSaves += 1;
+          logging::debug("Save at step {} skipped: the previous images are still being written", step);
+        } else {
+          Trace t("save_images");
+          hostProcessing.waitForCompletion();
+          saveBuffer ^= 1;
+          AccumulatedImage& target = films[saveBuffer];
+          gatherDeviceFilm(target);
+          if (uiServer) uiServer->startSendingRawImage(target.getHdrImage(), imageWidth, imageHeight, step, last);
+          if (!uiServer || last)
+            hostProcessing.run([&, step, exposure = state.exposure, gamma = state.gamma, filmPtr = &target]() {
+              Trace t("async_work");
+              filmPtr->saveImages(fileName, step, exposure, gamma);
+              logging::info("Saved images at step {}", step);
+            });
+        }
       }
     }
 
@@ -373,6 +447,8 @@ RenderSummary PathTracerApp::execute() {
   }
 
   hostProcessing.waitForCompletion();
+  nvtxRangePop();      // rendering
+  if (skippedSaves) logging::info("{} save interval(s) were skipped because the previous images were still being written", skippedSaves);
   if (uiServer) { uiServer->waitForRawImage(); uiServer.reset(); }
   if (recordStream && loadBalanceEnabled) {
     // the inactive list was re-dealt for a step that never ran: nothing to do, the film is complete

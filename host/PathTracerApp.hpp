@@ -52,6 +52,8 @@ private:
   bool loadNifModels(const std::string& assetPath);
   void createContexts(std::uint32_t width, std::uint32_t height, std::size_t itemsPerGpu);
   void check(int rc, Gpu& g, const char* what);
+  std::vector<int> deviceList() const;
+  void initFilmGatherComms();
   void initFilmGather(std::size_t floats);
   void gatherDeviceFilm(AccumulatedImage& film);
   /// Stop / detach / (reload NIF and) restart decision for a changed UI state (PathTracerApp.cpp:531-564).

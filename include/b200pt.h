@@ -118,6 +118,20 @@ int b200pt_set_render_settings(b200pt_ctx* ctx, uint64_t seed, float aa_scale_px
  * of the uploaded records seed the device accumulators (the reference host zeroes them). */
 int b200pt_setup(b200pt_ctx* ctx, const b200pt_trace_record* worklist, size_t n);
 
+/* The reference double-buffers its work list so that the host prepares list k+1 while the device renders list k
+ * (PathTracerApp.cpp:703-709). b200pt_setup_next is that second buffer: it starts the upload of the NEXT step's work
+ * list on a copy stream and returns at once, also while a path_trace is in flight; the list becomes the active one
+ * at the next b200pt_path_trace (which therefore must come after the b200pt_read_results of the running step).
+ * `worklist` must stay valid and unmodified until that path_trace call has returned; page-locked memory
+ * (b200pt_host_alloc) makes the copy truly asynchronous. A later b200pt_setup discards a staged list. */
+int b200pt_setup_next(b200pt_ctx* ctx, const b200pt_trace_record* worklist, size_t n);
+
+/* Page-locked host memory for work lists and results, the counterpart of the host buffers the reference connects to
+ * its streams (PathTracerApp.cpp:587-603). Pageable pointers are accepted everywhere; with these the 20-byte-record
+ * transfers of setup / read_results run at the full host-link rate and do not block the calling thread. */
+int b200pt_host_alloc(void** out, size_t bytes);
+int b200pt_host_free(void* p);
+
 /* "path_trace" (PathTracerApp.cpp:432-468,693): samples_per_step iterations of
  * camera ray -> path -> escaped-ray uv -> NIF -> accumulate, with no host involvement.
  * Asynchronous: returns once the work is enqueued; b200pt_sync waits for it.

@@ -7,6 +7,6 @@ from .load_balancer import (PAD_COORD, TRACE_RECORD, allocate_work_by_path_lengt
                             create_work_list_for_image, pad_work_list, shard_tiles)
 from .nif import NifMetaData, NifModel, load_assets, read_nif_bin, synthetic_model, write_nif_bin
 from .tracer import (AA_NOISE_TYPES, AA_NORMAL, AA_TRUNCATED_NORMAL, AA_UNIFORM, NIF_AUTO, NIF_SIMT, NIF_TCGEN05,
-                     B200PTError, Counters, PathTracer)
+                     B200PTError, Counters, PathTracer, PinnedRecords)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

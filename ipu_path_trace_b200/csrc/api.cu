@@ -102,6 +102,8 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     }
     if (const char* ov = getenv("B200PT_OVERLAP")) c->overlap = std::atoi(ov) != 0;
   }
+  if ((e = cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  if ((e = cudaEventCreateWithFlags(&c->evNextUploaded, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&c->evBegin)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&c->evEnd)) != cudaSuccess) return bail(e, "cudaEventCreate");
 
@@ -153,6 +155,9 @@ void b200pt_destroy(b200pt_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->cfg.device);
   if (c->traceStream) cudaStreamSynchronize(c->traceStream);
+  if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
+  if (c->evNextUploaded) cudaEventDestroy(c->evNextUploaded);
+  c->recStagingNext.release();
   if (c->stream) cudaStreamSynchronize(c->stream);
   for (cudaEvent_t e : c->evPool) cudaEventDestroy(e);
   for (int i = 0; i < 2; ++i) { if (c->evQueueFree[i]) cudaEventDestroy(c->evQueueFree[i]); if (c->evTraced[i]) cudaEventDestroy(c->evTraced[i]); }

@@ -62,18 +62,54 @@ int b200pt_set_sample_index(b200pt_ctx* c, uint32_t next) {
   return B200PT_OK;
 }
 
+// true if `p` is page-locked (cudaHostAlloc / cudaHostRegister): cudaMemcpyAsync then neither stages nor blocks
+static bool isPinned(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost;
+}
+
+int b200pt_host_alloc(void** out, size_t bytes) {
+  if (!out) return B200PT_ERR_INVALID;
+  *out = nullptr;
+  if (bytes == 0) return B200PT_OK;
+  return cudaHostAlloc(out, bytes, cudaHostAllocPortable) == cudaSuccess ? B200PT_OK : B200PT_ERR_CUDA;
+}
+
+int b200pt_host_free(void* p) {
+  if (!p) return B200PT_OK;
+  return cudaFreeHost(p) == cudaSuccess ? B200PT_OK : B200PT_ERR_CUDA;
+}
+
+int b200pt_setup_next(b200pt_ctx* c, const b200pt_trace_record* worklist, size_t n) {
+  if (!c) return B200PT_ERR_INVALID;
+  NvtxRange range("setup_next");
+  if (n > c->cfg.max_worklist) return c->fail(B200PT_ERR_INVALID, "setup_next: %zu work items exceed max_worklist %u", n, c->cfg.max_worklist);
+  if (n > 0 && !worklist) return c->fail(B200PT_ERR_INVALID, "setup_next: null worklist");
+  CU(c, cudaSetDevice(c->cfg.device));
+  CU(c, c->recStagingNext.ensure(c->cfg.max_worklist));
+  if (n > 0) CU(c, cudaMemcpyAsync(c->recStagingNext.p, worklist, n * sizeof(TraceRecord), cudaMemcpyHostToDevice, c->copyStream));
+  CU(c, cudaEventRecord(c->evNextUploaded, c->copyStream));
+  c->nextStaged = true;
+  c->nextItems = (uint32_t)n;
+  return B200PT_OK;
+}
+
 int b200pt_setup(b200pt_ctx* c, const b200pt_trace_record* worklist, size_t n) {
   if (!c) return B200PT_ERR_INVALID;
+  NvtxRange range("setup");
   if (n > c->cfg.max_worklist) return c->fail(B200PT_ERR_INVALID, "setup: %zu work items exceed max_worklist %u", n, c->cfg.max_worklist);
   if (n > 0 && !worklist) return c->fail(B200PT_ERR_INVALID, "setup: null worklist");
   CU(c, cudaSetDevice(c->cfg.device));
   static_assert(sizeof(b200pt_trace_record) == sizeof(TraceRecord), "record layouts must agree");
   c->nItems = (uint32_t)n;
+  c->nextStaged = false;                       // an explicit setup supersedes a staged list
   if (n == 0) return B200PT_OK;
   CU(c, cudaMemcpyAsync(c->recStaging.p, worklist, n * sizeof(TraceRecord), cudaMemcpyHostToDevice, c->stream));
   CU(c, launchUnpackRecords(c->recStaging.p, (uint32_t)n, c->pix.p, c->accum.p, c->sampleCount.p, c->pathLength.p, c->stream));
-  // the host buffer may be pageable: make sure the copy has consumed it before returning
-  CU(c, cudaStreamSynchronize(c->stream));
+  // A pageable host buffer has been consumed when cudaMemcpyAsync returns (the driver stages it); a page-locked one is
+  // read by the copy engine later, so wait for the copy - the caller owns the buffer again when setup returns.
+  if (isPinned(worklist)) CU(c, cudaStreamSynchronize(c->stream));
   return B200PT_OK;
 }
 
@@ -82,8 +118,16 @@ int b200pt_path_trace(b200pt_ctx* c) {
   int rc = requireSettings(c);
   if (rc) return rc;
   if (!c->nifLoaded) return c->fail(B200PT_ERR_STATE, "path_trace: no NIF weights uploaded");
+  NvtxRange range("path_trace");
   CU(c, cudaSetDevice(c->cfg.device));
   if (c->pending) { CU(c, cudaStreamSynchronize(c->stream)); rc = foldCounters(c); if (rc) return rc; }
+  if (c->nextStaged) {
+    // the list staged by setup_next becomes the active one: unpack it once its upload has landed
+    c->nextStaged = false;
+    c->nItems = c->nextItems;
+    CU(c, cudaStreamWaitEvent(c->stream, c->evNextUploaded, 0));
+    if (c->nItems) CU(c, launchUnpackRecords(c->recStagingNext.p, c->nItems, c->pix.p, c->accum.p, c->sampleCount.p, c->pathLength.p, c->stream));
+  }
   c->evUsed = 0; c->spans.clear();
   c->counters = b200pt_counters{};
   CU(c, cudaMemsetAsync(c->stats.p, 0, 4 * sizeof(unsigned long long), c->stream));
@@ -161,6 +205,7 @@ int b200pt_read_results(b200pt_ctx* c, b200pt_trace_record* out, size_t n, b200p
   if (!c) return B200PT_ERR_INVALID;
   if (n > c->nItems) return c->fail(B200PT_ERR_INVALID, "read_results: %zu items requested, %u uploaded", n, c->nItems);
   if (n > 0 && !out) return c->fail(B200PT_ERR_INVALID, "read_results: null buffer");
+  NvtxRange range("read_results");
   CU(c, cudaSetDevice(c->cfg.device));
   if (n > 0) {
     CU(c, launchPackRecords(c->recStaging.p, (uint32_t)n, c->pix.p, c->accum.p, c->sampleCount.p, c->pathLength.p, c->stream));
@@ -176,6 +221,7 @@ int b200pt_read_results(b200pt_ctx* c, b200pt_trace_record* out, size_t n, b200p
 
 int b200pt_film_accumulate(b200pt_ctx* c) {
   if (!c) return B200PT_ERR_INVALID;
+  NvtxRange range("accumulate_framebuffers");
   CU(c, cudaSetDevice(c->cfg.device));
   CU(c, launchFilmAccumulate(c->nItems, c->pix.p, c->accum.p, c->sampleCount.p, c->pathLength.p, c->film.p, c->cfg.width,
                              c->cfg.height, c->stream));

@@ -65,6 +65,12 @@ struct b200pt_ctx {
   // worklist (SoA) and accumulators
   uint32_t nItems = 0;
   DevBuf<TraceRecord> recStaging;
+  // setup_next: the next step's work list is uploaded on copyStream into recStagingNext while path_trace runs
+  DevBuf<TraceRecord> recStagingNext;
+  cudaStream_t copyStream = nullptr;
+  cudaEvent_t evNextUploaded = nullptr;
+  bool nextStaged = false;
+  uint32_t nextItems = 0;
   DevBuf<uint32_t> pix, sampleCount, pathLength;
   DevBuf<float4> accum;
   // wavefront queue
@@ -113,6 +119,14 @@ struct b200pt_ctx {
     if (e == cudaSuccess) return B200PT_OK;
     return fail(B200PT_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
   }
+};
+
+// NVTX ranges named after the reference's PVTI tracepoints (PathTracerApp.cpp:606-607,690-761); header-only, a no-op
+// unless a tool (nsys) is attached.
+#include <nvtx3/nvToolsExt.h>
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
 };
 
 #define CU(ctx, call) do { int rc_ = (ctx)->cuda((call), #call); if (rc_) return rc_; } while (0)

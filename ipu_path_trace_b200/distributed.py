@@ -94,11 +94,16 @@ class DistributedRenderer:
                 self._film = self._device_tensor(self.height * self.width * 3)
             else:
                 self._film = torch.zeros(self.height * self.width * 3, dtype=torch.float32, device=f"cuda:{self.local}")
+                # the library writes this tensor from its own (non-blocking) stream: torch's zero-fill must have landed
+                torch.cuda.synchronize(self._film.device)
         if self._film.is_cuda:
-            self.tracer.film_read_device(self._film.data_ptr(), scale)
+            self.tracer.film_read_device(self._film.data_ptr(), scale)      # synchronises the library's stream
         else:
             self._film.copy_(torch.from_numpy(self.tracer.film_read(scale).reshape(-1)))
         out = gather_film(self._film)
+        if self._film.is_cuda:
+            # NCCL's reduce is asynchronous on every rank: the next gather must not overwrite the send buffer under it
+            torch.cuda.synchronize(self._film.device)
         if out is None:
             return None
         return out.detach().cpu().numpy().reshape(self.height, self.width, 3)

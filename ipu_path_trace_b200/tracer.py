@@ -45,6 +45,33 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+class PinnedRecords:
+    """A TraceRecord array in page-locked host memory (b200pt_host_alloc): the host side of setup / read_results at the
+    full host-link rate. `.array` is a numpy view; the memory is released by close() or with the object."""
+
+    def __init__(self, n: int):
+        self.lib = _lib.load()
+        p = C.c_void_p()
+        rc = self.lib.b200pt_host_alloc(C.byref(p), C.c_size_t(max(1, n) * TRACE_RECORD.itemsize))
+        if rc != 0 or not p.value:
+            raise B200PTError(f"b200pt_host_alloc failed ({rc})")
+        self.ptr = p
+        buf = (C.c_ubyte * (n * TRACE_RECORD.itemsize)).from_address(p.value)
+        self.array = np.frombuffer(buf, dtype=TRACE_RECORD, count=n)
+
+    def close(self):
+        if self.ptr is not None:
+            self.array = None
+            self.lib.b200pt_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class PathTracer:
     """One context = one GPU (`--ipus N` of the reference becomes N contexts, one per GPU)."""
 
@@ -103,8 +130,20 @@ class PathTracer:
         self._check(self.lib.b200pt_setup(self.h, _ptr(wl), len(wl)), "setup")
         self.n_items = len(wl)
 
+    def setup_next(self, worklist: np.ndarray):
+        """Stage the NEXT step's work list while a path_trace may be in flight (the reference's double-buffered work list,
+        PathTracerApp.cpp:703-709); it becomes active at the next path_trace. `worklist` must stay alive and unmodified until
+        then - a reference is kept here."""
+        wl = np.ascontiguousarray(worklist, dtype=TRACE_RECORD)
+        self._staged = wl
+        self._check(self.lib.b200pt_setup_next(self.h, _ptr(wl), len(wl)), "setup_next")
+        self._staged_items = len(wl)
+
     def path_trace(self, sync: bool = True):
+        if getattr(self, "_staged", None) is not None:
+            self.n_items = self._staged_items
         self._check(self.lib.b200pt_path_trace(self.h), "path_trace")
+        self._staged = None
         if sync:
             self.sync()
 

@@ -1,0 +1,85 @@
+"""Multi-GPU parity on real devices (VERDICT r1 missing 8): the image rendered by 2 GPUs - through the torchrun
+DistributedRenderer (one rank per GPU, NCCL reduce of the disjoint-support films) and through the C++ host's `--ipus 2`
+(two contexts in one process, ncclReduce) - equals the 1-GPU image, and the per-rank counters add up to W*H*spp
+(the reference's multi-IPU replicas, src/PathTracerApp.cpp:205-252). Skipped on a box with fewer than 2 GPUs."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "host")
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def _gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _single_gpu_film(pt, model, W, H, sps, steps):
+    t = pt.PathTracer(W, H, nif_impl=pt.NIF_TCGEN05)
+    t.init_nif_weights(model)
+    t.init_render_settings(seed=1, samples_per_step=sps)
+    t.setup(pt.create_work_list_for_image(W, H))
+    tot = [0, 0, 0]
+    for _ in range(steps):
+        t.path_trace(sync=False)
+        t.film_accumulate()
+        c = t.counters()
+        tot[0] += c.paths; tot[1] += c.escaped; tot[2] += c.path_segments
+    film = t.film_read(1.0 / steps)
+    t.close()
+    return film, tot
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_torchrun_ranks_render_the_single_gpu_image(lib_built, nif_model, tmp_path, world):
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs, this box has {_gpus()}")
+    W, H, sps, steps = 208, 160, 8, 3
+    want, tot = _single_gpu_film(lib_built, nif_model, W, H, sps, steps)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "multi_rank_worker.py"), str(tmp_path), str(W), str(H), str(sps), str(steps)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    ranks = [json.load(open(tmp_path / f"rank{k}.json")) for k in range(world)]
+    assert sum(x["paths"] for x in ranks) == W * H * sps * steps == tot[0]
+    assert sum(x["escaped"] for x in ranks) == tot[1] and sum(x["segments"] for x in ranks) == tot[2]     # bit-exact discrete decisions
+    assert all(x["items"] > 0 for x in ranks)
+    got = np.load(tmp_path / "film.npy")
+    assert got.shape == (H, W, 3)
+    np.testing.assert_allclose(got, want, rtol=2e-6, atol=1e-7)       # fp32 atomics: addition order only
+
+
+def test_cli_two_gpus_equal_one(lib_built, nif_model, tmp_path):
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    import cv2
+    from test_gpu_host_cli import _assets
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    subprocess.run(["make", "-C", HOST, "b200_path_trace"], check=True, capture_output=True)
+    cli = os.path.join(HOST, "b200_path_trace")
+    assets = _assets(tmp_path, nif_model)
+    imgs = {}
+    for n in (1, 2):
+        for extra in ([], ["--host-film"]):
+            out = str(tmp_path / f"n{n}{'h' if extra else 'd'}.png")
+            r = subprocess.run([cli, "-o", out, "--assets", assets, "-w", "208", "-h", "160", "-s", "24", "--samples-per-step", "8",
+                                "--save-interval", "3", "--ipus", str(n)] + extra, capture_output=True, text=True, timeout=300)
+            assert r.returncode == 0, r.stderr[-2000:]
+            assert f"Created worklists for {n} GPUs" in r.stderr
+            imgs[(n, bool(extra))] = (cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED).astype(np.float64), cv2.imread(out, cv2.IMREAD_UNCHANGED))
+    base = imgs[(1, False)]
+    for key, (exr, png) in imgs.items():
+        np.testing.assert_allclose(exr, base[0], rtol=3e-6, atol=1e-7, err_msg=str(key))
+        assert np.abs(png.astype(int) - base[1].astype(int)).max() <= 1, key

@@ -128,3 +128,46 @@ def test_uint16_wrap_like_reference(lib_built, nif_model):
     assert ctr.paths == 64 * (65536 + 3)
     assert np.all(out["sampleCount"] == 3)
     t.close()
+
+
+def test_setup_next_and_pinned_buffers_equal_the_serial_programs(lib_built, nif_model):
+    """b200pt_setup_next (the reference's second work-list buffer, PathTracerApp.cpp:703-709) staged while path_trace runs,
+    with page-locked host buffers (b200pt_host_alloc), must give exactly the records of the serial setup / path_trace /
+    read_results sequence - including a different list at every step (here: the two halves of the image alternate)."""
+    W, H, sps = 96, 64, 4
+    full = lib_built.create_work_list_for_image(W, H)
+    lists = [full[: len(full) // 2], full[len(full) // 2:]]
+
+    def serial():
+        t = lib_built.PathTracer(W, H, nif_impl=lib_built.NIF_SIMT)
+        t.init_nif_weights(nif_model); t.init_render_settings(samples_per_step=sps)
+        outs = []
+        for k in range(4):
+            t.setup(lists[k & 1]); t.path_trace(); outs.append(t.read_results()[0].copy())
+        t.close()
+        return outs
+
+    def pipelined():
+        t = lib_built.PathTracer(W, H, nif_impl=lib_built.NIF_SIMT)
+        t.init_nif_weights(nif_model); t.init_render_settings(samples_per_step=sps)
+        pins = [lib_built.PinnedRecords(len(l)) for l in lists]
+        for p, l in zip(pins, lists):
+            p.array[:] = l
+        out = lib_built.PinnedRecords(len(lists[0]))
+        outs = []
+        t.setup(pins[0].array)
+        for k in range(4):
+            t.path_trace(sync=False)
+            if k < 3:
+                t.setup_next(pins[(k + 1) & 1].array)
+            outs.append(t.read_results(out.array)[0].copy())
+        t.close()
+        for p in pins + [out]:
+            p.close()
+        return outs
+    a, b = serial(), pipelined()
+    for x, y in zip(a, b):
+        assert np.array_equal(x["u"], y["u"]) and np.array_equal(x["v"], y["v"])
+        assert np.array_equal(x["pathLength"], y["pathLength"]) and np.array_equal(x["sampleCount"], y["sampleCount"])
+        np.testing.assert_allclose(_rgb(x), _rgb(y), rtol=1e-5, atol=1e-6)
+    assert not np.array_equal(a[0]["u"], a[1]["u"])
