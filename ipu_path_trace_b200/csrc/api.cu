@@ -134,6 +134,16 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     if ((e = c->qThrSlotB.alloc(cap * spl)) != cudaSuccess) return bail(e, "cudaMalloc queue");
   }
   if ((e = c->qCount.alloc(4)) != cudaSuccess) return bail(e, "cudaMalloc");
+  if (const char* tv = getenv("B200PT_TRACE")) {                   // A/B runs only
+    if (!std::strcmp(tv, "v1")) c->traceVariant = 1;
+    else if (!std::strcmp(tv, "v2")) c->traceVariant = 2;
+    else if (!std::strncmp(tv, "v2p", 3)) c->traceVariant = 10 + std::max(1, std::min(8, std::atoi(tv + 3)));
+  }
+  if (c->traceVariant != 1) {
+    const size_t entries = traceScratchEntries((uint32_t)cap);
+    if ((e = c->liveScratch.alloc(entries)) != cudaSuccess) return bail(e, "cudaMalloc live-ray list");
+    if ((e = c->escScratch.alloc(entries * 2)) != cudaSuccess) return bail(e, "cudaMalloc escape list");
+  }
   if ((e = c->stats.alloc(4)) != cudaSuccess) return bail(e, "cudaMalloc");
   const size_t filmN = (size_t)cfg->width * cfg->height * 3;
   if ((e = c->film.alloc(filmN)) != cudaSuccess) return bail(e, "cudaMalloc film");
@@ -167,6 +177,7 @@ void b200pt_destroy(b200pt_ctx* c) {
   if (c->evEnd) cudaEventDestroy(c->evEnd);
   c->recStaging.release(); c->pix.release(); c->sampleCount.release(); c->pathLength.release(); c->accum.release();
   c->qUv.release(); c->qThrSlot.release(); c->qCount.release(); c->stats.release();
+  c->liveScratch.release(); c->escScratch.release();
   c->scene.release(); c->film.release(); c->filmOut.release(); c->film8.release();
   for (auto& s : c->scratch) s.release();
   c->simtParams.release(); c->tcStream.release(); c->tcBias.release(); c->tcFeatTable.release();

@@ -77,6 +77,13 @@ struct b200pt_ctx {
   DevBuf<float2> qUv, qUvB;             // two queues: one being filled while the other is shaded
   DevBuf<float4> qThrSlot, qThrSlotB;
   DevBuf<uint32_t> qCount;               // [0], [1]: row counts of the two queues
+  // trace kernel v2: per-block live-ray and escape lists (trace_kernels.cu)
+  DevBuf<uint4> liveScratch;
+  DevBuf<float4> escScratch;
+  // B200PT_TRACE selects the path-tracing kernel: "v1" (default) one thread carries a path per sample; "v2" live-ray
+  // compaction + regeneration (bit-identical, measured slower on this scene: profiles/r2_trace_v2_ab.md); "v2p<k>" = v2
+  // with k phase-2 warps.
+  int traceVariant = 1;
   DevBuf<unsigned long long> stats;
   // film
   DevBuf<SceneSoA> scene;

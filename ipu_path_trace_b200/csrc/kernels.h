@@ -13,7 +13,10 @@ namespace b2 {
 // ---- path tracing (trace_kernels.cu) -----------------------------------------------------
 cudaError_t launchTraceWavefront(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                                  float2* qUv, float4* qThrSlot, uint32_t* qCount, uint32_t* sampleCount,
-                                 uint32_t* pathLength, unsigned long long* stats, cudaStream_t stream);
+                                 uint32_t* pathLength, unsigned long long* stats, uint4* liveScratch, float4* escScratch, int variant,
+                                 cudaStream_t stream);
+// entries of the live-ray list (uint4 each) and of the escape list (2 x float4 each) for up to maxItems work items
+size_t traceScratchEntries(uint32_t maxItems);
 cudaError_t launchTraceItems(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sample, int32_t* escaped, float* uv2,
                              float* thr3, int32_t* length, uint16_t* cam2, cudaStream_t stream);
 cudaError_t launchTraceFixed(const SceneSoA* scene, const DeviceSettings& s, uint32_t n, const uint16_t* cam2, const uint16_t* uniforms, uint32_t perPath, int32_t* escaped,

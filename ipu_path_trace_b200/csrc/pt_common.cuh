@@ -91,6 +91,11 @@ struct PathRng {
   uint32_t w0, w1, w2, w3;
   __device__ __forceinline__ PathRng(uint32_t seedLo, uint32_t seedHi, uint32_t pixelId, uint32_t sampleIdx)
       : pixel(pixelId), sample(sampleIdx), k0(seedLo), k1(seedHi), block(0), next(0) { refill(); }
+  // Resume a stream inside block 0 without recomputing it: the last two words of the block (the first two fed the
+  // anti-alias noise) travel with a live ray between the two phases of the wavefront kernel.
+  struct Resume {};
+  __device__ __forceinline__ PathRng(Resume, uint32_t seedLo, uint32_t seedHi, uint32_t pixelId, uint32_t sampleIdx, uint32_t word2, uint32_t word3)
+      : pixel(pixelId), sample(sampleIdx), k0(seedLo), k1(seedHi), block(0), next(2), w0(0), w1(0), w2(word2), w3(word3) {}
   __device__ __forceinline__ void refill() {
     const Philox4 p = philox4x32_10(pixel, sample, block, 0u, k0, k1);
     w0 = p.v[0]; w1 = p.v[1]; w2 = p.v[2]; w3 = p.v[3];

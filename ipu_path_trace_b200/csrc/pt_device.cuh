@@ -311,4 +311,51 @@ __device__ __forceinline__ PathResult tracePath(float camX, float camY, const De
   return res;
 }
 
+// One iteration of the loop above as a step of a per-lane state machine (the wavefront kernel regenerates a lane from
+// the live-ray list as soon as its path ends, instead of letting it idle until the longest path of the warp is done).
+// Same operations in the same order as tracePath, so the two agree bit for bit.
+struct PathState {
+  V3 o, d, thr;
+  uint32_t depth;
+  int count;
+};
+enum : int { kPathLive = 0, kPathEnded = 1, kPathEscaped = 2 };
+
+template <class Draw>
+__device__ __forceinline__ int pathBounce(PathState& p, const DeviceSettings& s, const SceneSoA& sc, Draw&& draw) {
+  float rr = 1.f;
+  if (p.depth >= s.rouletteDepth) {             // light.hpp:25-29
+    const float rnd = draw();
+    if (rnd <= s.stopProb) {
+      if (p.count == 0) p.count = 1;            // END overwrites the last record (:219-222)
+      return kPathEnded;
+    }
+    rr = s.rouletteWeight;
+  }
+  V3 n;
+  const int hit = closestHit(sc, p.o, p.d, n);
+  if (hit < 0) {                                // ESCAPED record {dir, rr}
+    p.thr = scale(p.thr, rr);
+    p.count += 1;
+    return kPathEscaped;
+  }
+  const int bsdf = sc.bsdf[hit];
+  if (bsdf == 0) {
+    const float u1 = draw();
+    const float u2 = draw();
+    const float w = sampleDiffuse(p.d, n, rr, u1, u2);
+    p.thr = scale(mul(p.thr, v3(sc.colr[hit], sc.colg[hit], sc.colb[hit])), w);
+  } else if (bsdf == 1) {
+    sampleMirror(p.d, n);
+    p.thr = scale(p.thr, rr);
+  } else {
+    const bool through = sampleGlass(p.d, n, s.refractiveIndex, draw());
+    const V3 c = through ? v3(sc.colr[hit], sc.colg[hit], sc.colb[hit]) : v3(1.f, 1.f, 1.f);
+    p.thr = scale(mul(p.thr, c), 1.15f * rr);
+  }
+  p.count += 1;
+  p.depth += 1;
+  return p.count == (int)s.maxPathLength ? kPathEnded : kPathLive;
+}
+
 } // namespace b2

@@ -170,4 +170,4 @@ def test_setup_next_and_pinned_buffers_equal_the_serial_programs(lib_built, nif_
         assert np.array_equal(x["u"], y["u"]) and np.array_equal(x["v"], y["v"])
         assert np.array_equal(x["pathLength"], y["pathLength"]) and np.array_equal(x["sampleCount"], y["sampleCount"])
         np.testing.assert_allclose(_rgb(x), _rgb(y), rtol=1e-5, atol=1e-6)
-    assert not np.array_equal(a[0]["u"], a[1]["u"])
+    assert not np.array_equal(a[0]["v"], a[1]["v"])

@@ -98,3 +98,37 @@ def test_call_order_errors(lib_built, nif_model):
     t.close()
     with pytest.raises(lib_built.B200PTError):
         lib_built.PathTracer(16, 16, roulette_depth=0)
+
+
+@pytest.mark.parametrize("variant", ["v2", "v2p3"])
+def test_live_ray_compaction_kernel_equals_default(lib_built, nif_model, monkeypatch, variant):
+    """B200PT_TRACE=v2: the trace kernel with live-ray compaction (warp ballot/prefix into a per-block live list) and path
+    regeneration (a lane takes the next live ray when its path ends) must reproduce the default kernel: per-item
+    sampleCount and pathLength, escaped / segment counters bit for bit, radiance up to the order of the fp32 atomics -
+    on a ragged work list with padding items, 9 samples per step (groups of 4 + 1) and two steps."""
+    W, H, sps = 200, 130, 9
+    wl = lib_built.create_work_list_for_image(W, H)
+    pad = np.zeros(37, dtype=wl.dtype); pad["u"] = 65535; pad["v"] = 65535
+    wl = np.concatenate([wl[:777], pad, wl[777:]])
+
+    def run(tv):
+        if tv:
+            monkeypatch.setenv("B200PT_TRACE", tv)
+        else:
+            monkeypatch.delenv("B200PT_TRACE", raising=False)
+        t = lib_built.PathTracer(W, H, max_worklist=len(wl))
+        t.init_nif_weights(nif_model)
+        t.init_render_settings(seed=5, samples_per_step=sps)
+        t.setup(wl)
+        t.path_trace(); t.path_trace()
+        out, ctr = t.read_results()
+        t.close()
+        return out, ctr
+    a, ca = run(None)
+    b, cb = run(variant)
+    assert (ca.paths, ca.escaped, ca.path_segments) == (cb.paths, cb.escaped, cb.path_segments)
+    assert ca.paths == W * H * sps                      # counters are those of the last path_trace
+    assert np.array_equal(a["sampleCount"], b["sampleCount"]) and np.array_equal(a["pathLength"], b["pathLength"])
+    assert np.all(b["sampleCount"][777:777 + 37] == 0)
+    rgb = lambda x: np.stack([x["r"], x["g"], x["b"]], 1).astype(np.float64)
+    np.testing.assert_allclose(rgb(a), rgb(b), rtol=1e-5, atol=1e-6)
