@@ -187,6 +187,79 @@ def run_reference(args) -> None:
 
 
 # ---------------------------------------------------------------------------------------------
+# Extras the driver can see: BASELINE configs C4 and C5, and the reference's own run-level metric
+# (the final `Samples/sec` line of PathTracerApp.cpp:782-791) through the C++ host with the README's command line.
+# ---------------------------------------------------------------------------------------------
+def c4_uv(n: int = 1 << 20, seed: int = 1234):
+    """BASELINE config C4: n unit directions uniform on the sphere (Philox seed 1234) -> equirectangular (u,v)
+    (codelets.cpp:333-347 in numpy; the microbenchmark only needs their distribution)."""
+    g = np.random.Generator(np.random.Philox(seed))
+    d = g.standard_normal((n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    u = np.arccos(np.clip(d[:, 1], -1, 1)) / np.pi
+    phi = np.arctan2(d[:, 2], d[:, 0])
+    phi[phi < 0] += 2 * np.pi
+    return u.astype(np.float32), (phi / (2 * np.pi)).astype(np.float32)
+
+
+def run_c4(tracer, flops_per_eval: int, reps: int = 20):
+    import torch
+    import ipu_path_trace_b200 as pt
+    u, v = c4_uv()
+    du, dv = torch.from_numpy(u).cuda(), torch.from_numpy(v).cuda()
+    out = torch.empty(3 * len(u), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    tracer.nif_infer_device(len(u), du.data_ptr(), dv.data_ptr(), out.data_ptr(), pt.NIF_TCGEN05, 3)          # warm-up
+    ms = tracer.nif_infer_device(len(u), du.data_ptr(), dv.data_ptr(), out.data_ptr(), pt.NIF_TCGEN05, reps) / reps
+    burst = None
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        burst = float(json.load(open(pk))["bf16_tflops"])
+    tf = len(u) * flops_per_eval / (ms * 1e-3) / 1e12
+    return {"workload": "C4: 1048576 escaped-ray directions (Philox 1234) through the 12-dim embedding + 6x320 fp16 MLP, resident in HBM",
+            "reps": reps, "ms_per_batch": ms, "rays_per_s": len(u) / (ms * 1e-3), "tflops": tf,
+            "frac_of_burst_peak": (tf / burst) if burst else None, "burst_peak_tflops": burst, "finite": bool(torch.isfinite(out).all())}
+
+
+def run_cli(n_gpus: int, width: int, height: int, spp: int, sps: int, save_interval: int, tag: str, timeout: float):
+    """host/b200_path_trace with the reference's command line (README.md:82); parses its log like a user would."""
+    import re
+    import tempfile
+    import ipu_path_trace_b200 as pt
+    from ipu_path_trace_b200.nif import write_nif_bin
+    exe = os.path.join(ROOT, "host", "b200_path_trace")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "b200_path_trace"], check=True, capture_output=True)
+    with tempfile.TemporaryDirectory() as tmp:
+        assets = os.path.join(tmp, "assets.extra")
+        os.makedirs(assets)
+        meta = os.path.join(ROOT, "tests", "golden", "nif_metadata.txt")        # the shipped model's metadata, verbatim
+        open(os.path.join(assets, "nif_metadata.txt"), "w").write(open(meta).read())
+        write_nif_bin(os.path.join(assets, "nif.bin"), pt.synthetic_model())
+        out = os.path.join(tmp, f"{tag}.png")
+        cmd = [exe, "-o", out, "--assets", assets, "-w", str(width), "-h", str(height), "-s", str(spp), "--samples-per-step", str(sps),
+               "--ipus", str(n_gpus), "--save-interval", str(save_interval)]
+        t0 = time.perf_counter()
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+        wall = time.perf_counter() - t0
+        log = r.stderr
+        if r.returncode != 0:
+            return {"error": log[-400:], "cmd": " ".join(cmd[:1] + cmd[5:])}
+        steps = [(float(a), float(b)) for a, b in re.findall(r"Completed render step \d+/\d+ in ([0-9.e+-]+) seconds \(Samples/sec ([0-9.e+-]+)\)", log)]
+        final = re.findall(r"\] Samples/sec: ([0-9.e+-]+)", log)
+        init = re.findall(r"Initialisation took ([0-9.e+-]+) seconds", log)
+        secs = np.array([a for a, _ in steps])
+        rates = np.array([b for _, b in steps])
+        files_ok = os.path.exists(out) and os.path.exists(out[:-4] + ".exr")
+        return {"cmd": "b200_path_trace " + " ".join(cmd[5:]), "steps": len(steps), "run_level_samples_per_s": float(final[-1]) if final else None,
+                "steady_state_samples_per_s": float(np.median(rates)) if len(rates) else None,
+                "run_level_over_steady_state": (float(final[-1]) / float(np.median(rates))) if final and len(rates) else None,
+                "initialisation_s": float(init[-1]) if init else None, "process_wall_s": wall,
+                "slowest_step_over_median": float(secs.max() / np.median(secs)) if len(secs) else None,
+                "saves": log.count("Saved images at step"), "png_and_exr_written": files_ok}
+
+
+# ---------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------
 def run_ours(args) -> None:
@@ -203,6 +276,14 @@ def run_ours(args) -> None:
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # host-side barrier for the extras: an NCCL barrier would leave a spinning kernel on every idle rank's GPU, time-slicing
+    # against the C++ host process that renders on those GPUs meanwhile
+    cpu_group = dist.new_group(backend="gloo") if dist is not None else None
+
+    def host_barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier(group=cpu_group)
 
     def barrier():
         if dist is not None:
@@ -296,6 +377,29 @@ def run_ours(args) -> None:
     total, e2e_total, nif_ms, trace_ms, dev_ms, gather_ms = stats.tolist()
     escaped, paths, launches = sums.tolist()
 
+    extras = {}
+    if rank == 0 and not args.no_extras:
+        try:
+            extras["c4"] = run_c4(tracer, flops_per_eval)
+        except Exception as e:      # an extra must never lose the headline
+            extras["c4"] = {"error": repr(e)[:300]}
+    tracer.close()
+    tracer = None
+    pin_in.close(); pin_out.close()
+    del flush, film_dev
+    torch.cuda.empty_cache()
+    host_barrier()
+    if rank == 0 and not args.no_extras:
+        # the reference's README run, to completion, through the C++ host on the same GPUs (the ranks idle meanwhile)
+        try:
+            extras["cli_c2"] = run_cli(world, W, H, args.cli_spp, SAMPLES_PER_STEP, SAVE_INTERVAL, "c2", timeout=900)
+            if world == 8:
+                extras["cli_c5"] = run_cli(world, 3840, 2160, 6400, 64, 10, "c5", timeout=600)
+                extras["cli_c5"]["workload"] = "C5: 3840x2160 progressive render, PNG+EXR every 10 steps of 64 samples, 8 GPUs"
+        except Exception as e:
+            extras["cli_c2"] = {"error": repr(e)[:300]}
+    host_barrier()
+
     if rank == 0:
         samples_per_job_step = W * H * sps
         value = samples_per_job_step * args.steps / total
@@ -324,12 +428,11 @@ def run_ours(args) -> None:
                          "traffic": nif_traffic_bytes(), "kernel": "nif_tc_kernel", "peak_source": peak_src,
                          "whole_step_frac": (flops_per_eval * escaped / world) / (dev_ms * 1e-3) / 1e12 / peak_tf if dev_ms > 0 else 0.0},
         }
+        line["config"].update(extras)
         if world == 1 and not args.no_cpu_baseline:
             v, desc, cores = cpu_sample_run(15.0)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
         print(json.dumps(line), flush=True)
-    tracer.close()
-    pin_in.close(); pin_out.close()
     if dist is not None:
         dist.destroy_process_group()
 
@@ -342,6 +445,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--samples-per-step", type=int, default=SAMPLES_PER_STEP)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C4 microbenchmark and the C++ host runs (config.c4 / cli_c2 / cli_c5)")
+    ap.add_argument("--cli-spp", type=int, default=100000, help="samples per pixel of the C++ host run (README.md:82 uses 100000)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":

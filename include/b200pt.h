@@ -108,6 +108,22 @@ const char* b200pt_version(void);
 /* "init_nif_weights" (NifModel.cpp:357-401; re-runnable mid-render, PathTracerApp.cpp:548-557). */
 int b200pt_upload_nif(b200pt_ctx* ctx, const b200pt_nif_desc* nif);
 
+/* The scene as data. The reference hard-codes its scene inside RayTraceKernel::compute and says so ("The scene is currently
+ * hard coded here", codelets.cpp:110; the struct comment at :90-92 anticipates passing it in). A context starts with that
+ * scene (5 spheres + 1 disc, no emitter); b200pt_set_scene replaces it: up to 16 spheres / discs with the reference's three
+ * materials, optionally emissive (light::Material, EMIT records: codelets.cpp:192-196). n = 0 restores the built-in scene.
+ * Takes effect at the next path_trace. */
+typedef struct b200pt_primitive {
+  int32_t shape;        /* 0 sphere (light::Sphere), 1 disc (light::Disc) */
+  int32_t material;     /* 0 diffuse, 1 specular, 2 refractive (light::Material::Type) */
+  float centre[3];
+  float normal[3];      /* disc only; normalised like light::Disc's constructor */
+  float radius;
+  float colour[3];
+  float emission[3];    /* emissive iff any component is non-zero */
+} b200pt_primitive;
+int b200pt_set_scene(b200pt_ctx* ctx, const b200pt_primitive* prims, uint32_t n);
+
 /* "init_render_settings" (PathTracerApp.cpp:333-355,587-595): seed, anti-alias scale in pixels
  * and field of view in radians (both streamed as half by the reference and rounded likewise
  * here), HDRI azimuth in radians, on-device sample count of one path_trace program. */
@@ -176,7 +192,9 @@ int b200pt_nif_infer_device(b200pt_ctx* ctx, size_t n, const void* u_dev, const 
 /* One wavefront of sample `sample` over the uploaded worklist WITHOUT shading: per work item
  * escaped flag, (u,v) of the env-map lookup, RGB path throughput, path length and the binary16
  * camera ray (GenerateCameraRays codelets.cpp:36-80, RayTraceKernel :93-227,
- * PreProcessEscapedRays :312-358). Host output arrays of n items; any may be NULL. */
+ * PreProcessEscapedRays :312-358). Host output arrays of n items; any may be NULL.
+ * escaped: 0 the path ended without light (END), 1 it escaped (uv2 valid, thr3 = throughput to multiply the environment
+ * radiance with), 2 it ended on an emitter of a b200pt_set_scene scene (thr3 = the radiance itself, no lookup). */
 int b200pt_trace_wavefront(b200pt_ctx* ctx, uint32_t sample, size_t n, int32_t* escaped, float* uv2,
                            float* throughput3, int32_t* length, uint16_t* cam_rays2);
 

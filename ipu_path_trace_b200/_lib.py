@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(HERE, "libb200pt.so")
 # Every symbol include/b200pt.h declares (tests check the library exports each one).
 EXPORTS = [
     "b200pt_create", "b200pt_destroy", "b200pt_last_error", "b200pt_version",
-    "b200pt_upload_nif", "b200pt_set_render_settings", "b200pt_setup", "b200pt_setup_next", "b200pt_host_alloc", "b200pt_host_free",
+    "b200pt_upload_nif", "b200pt_set_render_settings", "b200pt_setup", "b200pt_setup_next", "b200pt_host_alloc", "b200pt_host_free", "b200pt_set_scene",
     "b200pt_path_trace", "b200pt_sync",
     "b200pt_read_results", "b200pt_film_accumulate", "b200pt_film_clear", "b200pt_film_read",
     "b200pt_film_read_device", "b200pt_film_tonemap", "b200pt_set_sample_index", "b200pt_get_counters",
@@ -20,6 +20,11 @@ EXPORTS = [
     "b200pt_trace_fixed", "b200pt_kat",
     "b200pt_cornell_render", "b200pt_cornell_trace_paths", "b200pt_cornell_last_error",
 ]
+
+
+class Primitive(C.Structure):
+    _fields_ = [("shape", C.c_int32), ("material", C.c_int32), ("centre", C.c_float * 3), ("normal", C.c_float * 3),
+                ("radius", C.c_float), ("colour", C.c_float * 3), ("emission", C.c_float * 3)]
 
 
 class Config(C.Structure):
@@ -92,6 +97,7 @@ def load() -> C.CDLL:
     lib.b200pt_upload_nif.argtypes = [vp, C.POINTER(NifDesc)]
     lib.b200pt_set_render_settings.argtypes = [vp, C.c_uint64, f32, f32, f32, u32]
     lib.b200pt_setup.argtypes = [vp, vp, sz]
+    lib.b200pt_set_scene.argtypes = [vp, C.POINTER(Primitive), u32]
     lib.b200pt_setup_next.argtypes = [vp, vp, sz]
     lib.b200pt_host_alloc.argtypes = [C.POINTER(vp), sz]
     lib.b200pt_host_free.argtypes = [vp]

@@ -12,37 +12,45 @@ namespace {
 // The hard-coded scene of the reference (codelets.cpp:110-144): five spheres and a disc, colours
 // carry the 2x gain (:127-130), no emitters (:117,142). Double-typed literals of the reference
 // (-3.23, -0.19931) narrow to float exactly as (float)literal does.
-void buildScene(SceneSoA& sc) {
-  std::memset(&sc, 0, sizeof(sc));
-  int n = 0;
-  auto sphere = [&](float cx, float cy, float cz, float r, float cr, float cg, float cb, int bsdf) {
-    sc.shape[n] = 0; sc.bsdf[n] = bsdf;
-    sc.cx[n] = cx; sc.cy[n] = cy; sc.cz[n] = cz;
-    sc.nx[n] = 0.f; sc.ny[n] = 1.f; sc.nz[n] = 0.f;
-    sc.radius2[n] = r * r; sc.planeD[n] = 0.f;
-    sc.colr[n] = cr; sc.colg[n] = cg; sc.colb[n] = cb;
-    ++n;
-  };
-  const float gain = 2.f;
-  sphere(-1.8575f, -0.98714f, -3.6f, 0.6f, 1.f * gain, .89f * gain, .55f * gain, 0);
-  sphere(0.74795f, -0.55f, -4.3816f, 1.05f, 1.f, 1.f, 1.f, 1);
-  sphere(1.9929f, -1.08666f, (float)-3.23, 0.5f, 0.75f, 0.75f, 0.75f, 2);
-  sphere((float)-0.19931, -1.183f, -2.75f, 0.4f, .8f * gain, .06f * gain, .391f * gain, 0);
-  sphere((float)-0.19931, -1.183f, -2.75f, 0.4001f, 1.f, 1.f, 1.f, 2);
-  {   // Disc(normal (0,1,0), centre (0,-1.6,-5.22), radius 3.5): ctor normalises n, d = |c.n| (light.hpp:98-101)
-    const float nx = 0.f, ny = 1.f, nz = 0.f;
+int appendPrimitive(SceneSoA& sc, const b200pt_primitive& p) {
+  const int n = sc.count;
+  if (n >= kMaxPrims) return -1;
+  sc.shape[n] = p.shape; sc.bsdf[n] = p.material;
+  sc.cx[n] = p.centre[0]; sc.cy[n] = p.centre[1]; sc.cz[n] = p.centre[2];
+  sc.nx[n] = 0.f; sc.ny[n] = 1.f; sc.nz[n] = 0.f;
+  sc.radius2[n] = p.radius * p.radius; sc.planeD[n] = 0.f;
+  if (p.shape == 1) {   // Disc ctor normalises n, d = |c.n| (light.hpp:98-101)
+    const float nx = p.normal[0], ny = p.normal[1], nz = p.normal[2];
     const float inv = 1.f / std::sqrt(nx * nx + ny * ny + nz * nz);
     const float ux = nx * inv, uy = ny * inv, uz = nz * inv;
-    const float cx = 0.f, cy = -1.6f, cz = -5.22f;
-    sc.shape[n] = 1; sc.bsdf[n] = 0;
-    sc.cx[n] = cx; sc.cy[n] = cy; sc.cz[n] = cz;
     sc.nx[n] = ux; sc.ny[n] = uy; sc.nz[n] = uz;
-    sc.radius2[n] = 3.5f * 3.5f;
-    sc.planeD[n] = std::fabs(cx * ux + cy * uy + cz * uz);
-    sc.colr[n] = .98f * gain; sc.colg[n] = .76f * gain; sc.colb[n] = .66f * gain;
-    ++n;
+    sc.planeD[n] = std::fabs(p.centre[0] * ux + p.centre[1] * uy + p.centre[2] * uz);
   }
-  sc.count = n;
+  sc.colr[n] = p.colour[0]; sc.colg[n] = p.colour[1]; sc.colb[n] = p.colour[2];
+  sc.emr[n] = p.emission[0]; sc.emg[n] = p.emission[1]; sc.emb[n] = p.emission[2];
+  sc.emissive[n] = (p.emission[0] != 0.f || p.emission[1] != 0.f || p.emission[2] != 0.f) ? 1 : 0;
+  sc.count = n + 1;
+  return 0;
+}
+
+void buildScene(SceneSoA& sc) {
+  std::memset(&sc, 0, sizeof(sc));
+  auto prim = [&](int shape, float cx, float cy, float cz, float r, float cr, float cg, float cb, int bsdf) {
+    b200pt_primitive p{};
+    p.shape = shape; p.material = bsdf;
+    p.centre[0] = cx; p.centre[1] = cy; p.centre[2] = cz;
+    p.normal[0] = 0.f; p.normal[1] = 1.f; p.normal[2] = 0.f;
+    p.radius = r;
+    p.colour[0] = cr; p.colour[1] = cg; p.colour[2] = cb;
+    appendPrimitive(sc, p);
+  };
+  const float gain = 2.f;
+  prim(0, -1.8575f, -0.98714f, -3.6f, 0.6f, 1.f * gain, .89f * gain, .55f * gain, 0);
+  prim(0, 0.74795f, -0.55f, -4.3816f, 1.05f, 1.f, 1.f, 1.f, 1);
+  prim(0, 1.9929f, -1.08666f, (float)-3.23, 0.5f, 0.75f, 0.75f, 0.75f, 2);
+  prim(0, (float)-0.19931, -1.183f, -2.75f, 0.4f, .8f * gain, .06f * gain, .391f * gain, 0);
+  prim(0, (float)-0.19931, -1.183f, -2.75f, 0.4001f, 1.f, 1.f, 1.f, 2);
+  prim(1, 0.f, -1.6f, -5.22f, 3.5f, .98f * gain, .76f * gain, .66f * gain, 0);      // Disc(Y, (0,-1.6,-5.22), 3.5)
 }
 
 } // namespace
@@ -158,6 +166,31 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
   if ((e = cudaMemcpyAsync(c->scene.p, &scene, sizeof(scene), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) return bail(e, "scene upload");
   if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
   *out = c;
+  return B200PT_OK;
+}
+
+int b200pt_set_scene(b200pt_ctx* c, const b200pt_primitive* prims, uint32_t n) {
+  if (!c) return B200PT_ERR_INVALID;
+  if (n > (uint32_t)kMaxPrims) return c->fail(B200PT_ERR_INVALID, "set_scene: %u primitives exceed the limit of %d", n, kMaxPrims);
+  if (n > 0 && !prims) return c->fail(B200PT_ERR_INVALID, "set_scene: null primitive list");
+  SceneSoA scene;
+  if (n == 0) {
+    buildScene(scene);
+  } else {
+    std::memset(&scene, 0, sizeof(scene));
+    for (uint32_t i = 0; i < n; ++i) {
+      const b200pt_primitive& p = prims[i];
+      if (p.shape < 0 || p.shape > 1 || p.material < 0 || p.material > 2 || !(p.radius > 0.f))
+        return c->fail(B200PT_ERR_INVALID, "set_scene: primitive %u has an unknown shape/material or a non-positive radius", i);
+      if (p.shape == 1 && p.normal[0] == 0.f && p.normal[1] == 0.f && p.normal[2] == 0.f)
+        return c->fail(B200PT_ERR_INVALID, "set_scene: disc %u has a zero normal", i);
+      appendPrimitive(scene, p);
+    }
+  }
+  CU(c, cudaSetDevice(c->cfg.device));
+  CU(c, cudaStreamSynchronize(c->stream));          // a path_trace in flight keeps the scene it started with
+  if (c->traceStream) CU(c, cudaStreamSynchronize(c->traceStream));
+  CU(c, cudaMemcpy(c->scene.p, &scene, sizeof(scene), cudaMemcpyHostToDevice));
   return B200PT_OK;
 }
 

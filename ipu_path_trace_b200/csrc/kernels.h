@@ -13,7 +13,7 @@ namespace b2 {
 // ---- path tracing (trace_kernels.cu) -----------------------------------------------------
 cudaError_t launchTraceWavefront(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                                  float2* qUv, float4* qThrSlot, uint32_t* qCount, uint32_t* sampleCount,
-                                 uint32_t* pathLength, unsigned long long* stats, uint4* liveScratch, float4* escScratch, int variant,
+                                 uint32_t* pathLength, unsigned long long* stats, float* accum, uint4* liveScratch, float4* escScratch, int variant,
                                  cudaStream_t stream);
 // entries of the live-ray list (uint4 each) and of the escape list (2 x float4 each) for up to maxItems work items
 size_t traceScratchEntries(uint32_t maxItems);

@@ -44,8 +44,9 @@ struct DeviceSettings {
   int32_t aaNoiseType;
 };
 
-// Primitive table, SoA. 5 spheres + 1 disc (codelets.cpp:110-144); built on the host.
-constexpr int kMaxPrims = 8;
+// Primitive table, SoA; built on the host from the built-in scene (5 spheres + 1 disc, codelets.cpp:110-144) or from
+// b200pt_set_scene (the reference anticipates the scene as data, codelets.cpp:90-92).
+constexpr int kMaxPrims = 16;
 struct SceneSoA {
   int32_t count;
   int32_t shape[kMaxPrims];     // 0 sphere, 1 disc
@@ -55,6 +56,8 @@ struct SceneSoA {
   float radius2[kMaxPrims];
   float planeD[kMaxPrims];      // |centre . n| (light.hpp:101)
   float colr[kMaxPrims], colg[kMaxPrims], colb[kMaxPrims];
+  int32_t emissive[kMaxPrims];  // light.hpp Material::emissive
+  float emr[kMaxPrims], emg[kMaxPrims], emb[kMaxPrims];
 };
 
 // ------------------------------------------------------------------------------------------

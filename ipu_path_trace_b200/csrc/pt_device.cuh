@@ -252,9 +252,10 @@ __device__ __forceinline__ void escapedUv(V3 d, float azimuth, float& u, float& 
 
 struct PathResult {
   bool escaped;
+  bool emitted;     // the path ended on an emitter (EMIT record, codelets.cpp:192-196): pixel += throughput, no NIF lookup
   int length;       // records the reference would have written (END included)
   V3 dir;           // unit direction of the escaped ray
-  V3 throughput;    // pixel += throughput (*) L_env(dir)
+  V3 throughput;    // escaped: pixel += throughput (*) L_env(dir); emitted: throughput already holds emission (*) path weight
 };
 
 // codelets.cpp:159-223 for one camera ray. The reference pushes one Contribution per vertex
@@ -270,7 +271,7 @@ __device__ __forceinline__ PathResult tracePath(float camX, float camY, const De
   uint32_t depth = 0;
   int count = 0;
   const int maxLen = (int)s.maxPathLength;
-  bool lit = false;
+  bool lit = false, emit = false;
   while (count != maxLen) {
     float rr = 1.f;
     if (depth >= s.rouletteDepth) {             // light.hpp:25-29
@@ -284,6 +285,13 @@ __device__ __forceinline__ PathResult tracePath(float camX, float camY, const De
       thr = scale(thr, rr);
       count += 1;
       lit = true;
+      break;
+    }
+    if (sc.emissive[hit]) {                     // EMIT record {emission, rr} (codelets.cpp:192-196)
+      thr = mul(thr, scale(v3(sc.emr[hit], sc.emg[hit], sc.emb[hit]), rr));
+      count += 1;
+      lit = true;
+      emit = true;
       break;
     }
     const int bsdf = sc.bsdf[hit];
@@ -304,7 +312,8 @@ __device__ __forceinline__ PathResult tracePath(float camX, float camY, const De
     depth += 1;
   }
   if (!lit && count == 0) count = 1;            // END overwrites the last record (:219-222)
-  res.escaped = lit;
+  res.escaped = lit && !emit;
+  res.emitted = emit;
   res.length = count;
   res.dir = d;
   res.throughput = lit ? thr : v3(0.f, 0.f, 0.f);
@@ -319,7 +328,7 @@ struct PathState {
   uint32_t depth;
   int count;
 };
-enum : int { kPathLive = 0, kPathEnded = 1, kPathEscaped = 2 };
+enum : int { kPathLive = 0, kPathEnded = 1, kPathEscaped = 2, kPathEmitted = 3 };
 
 template <class Draw>
 __device__ __forceinline__ int pathBounce(PathState& p, const DeviceSettings& s, const SceneSoA& sc, Draw&& draw) {
@@ -338,6 +347,11 @@ __device__ __forceinline__ int pathBounce(PathState& p, const DeviceSettings& s,
     p.thr = scale(p.thr, rr);
     p.count += 1;
     return kPathEscaped;
+  }
+  if (sc.emissive[hit]) {                       // EMIT record {emission, rr}
+    p.thr = mul(p.thr, scale(v3(sc.emr[hit], sc.emg[hit], sc.emb[hit]), rr));
+    p.count += 1;
+    return kPathEmitted;
   }
   const int bsdf = sc.bsdf[hit];
   if (bsdf == 0) {

@@ -21,13 +21,21 @@ __device__ __forceinline__ void stageScene(SceneSoA& dst, const SceneSoA* __rest
 
 constexpr int kTraceThreads = 256;
 
+// A path that ended on an emitter (EMIT record, codelets.cpp:192-196) needs no NIF lookup: its radiance goes straight into the
+// work item's accumulator, with the same fp32 atomics the NIF kernel uses for escaped paths (nif_common.cuh nifEmit).
+__device__ __forceinline__ void emitRadiance(float* __restrict__ accum, uint32_t slot, V3 radiance) {
+  atomicAdd(accum + 4 * (size_t)slot, radiance.x);
+  atomicAdd(accum + 4 * (size_t)slot + 1, radiance.y);
+  atomicAdd(accum + 4 * (size_t)slot + 2, radiance.z);
+}
+
 // v1 (default): one thread carries a whole path per sample; lanes whose path has ended idle until the longest path of the
 // warp is done (ncu: 19.9 of 32 lanes per instruction); escaped rays are compacted with ballot/prefix per sample.
 __global__ void __launch_bounds__(kTraceThreads)
 trace_wavefront_kernel_v1(const SceneSoA* __restrict__ scene, const DeviceSettings s, const uint32_t* __restrict__ pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                        float2* __restrict__ qUv, float4* __restrict__ qThrSlot, uint32_t* __restrict__ qCount,
                        uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength,
-                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */) {
+                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */, float* __restrict__ accum) {
   __shared__ SceneSoA sc;
   __shared__ uint32_t warpCount[kTraceThreads / 32];
   __shared__ uint32_t blockBase;
@@ -58,6 +66,8 @@ trace_wavefront_kernel_v1(const SceneSoA* __restrict__ scene, const DeviceSettin
         esc = true;
         escapedUv(r.dir, s.azimuth, u, v);
         thr = r.throughput;
+      } else if (r.emitted) {
+        emitRadiance(accum, slot, r.throughput);
       }
     }
     // compaction: warp ballot -> block prefix -> one atomic per block
@@ -132,7 +142,7 @@ __global__ void __launch_bounds__(kTraceThreads)
 trace_wavefront_kernel(const SceneSoA* __restrict__ scene, const DeviceSettings s, const uint32_t* __restrict__ pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                        float2* __restrict__ qUv, float4* __restrict__ qThrSlot, uint32_t* __restrict__ qCount,
                        uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength,
-                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */,
+                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */, float* __restrict__ accum,
                        uint4* __restrict__ liveScratch, float4* __restrict__ escScratch, uint32_t phase2Warps) {
   __shared__ SceneSoA sc;
   __shared__ uint32_t warpCount[kTraceThreads / 32];
@@ -263,6 +273,7 @@ trace_wavefront_kernel(const SceneSoA* __restrict__ scene, const DeviceSettings 
         if (active) state = pathBounce(ps, s, sc, [&]() { return rng.uniformHalf(); });
         const bool done = active && state != kPathLive;
         const bool esc = active && state == kPathEscaped;
+        if (active && state == kPathEmitted) emitRadiance(accum, itemBase + local, ps.thr);
         if (done) { atomicAdd(&lenAcc[local], (uint32_t)ps.count); active = false; }
         const uint32_t em = __ballot_sync(0xffffffffu, esc);
         if (em) {
@@ -328,18 +339,19 @@ size_t traceScratchEntries(uint32_t maxItems) {
 
 cudaError_t launchTraceWavefront(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                                  float2* qUv, float4* qThrSlot, uint32_t* qCount, uint32_t* sampleCount,
-                                 uint32_t* pathLength, unsigned long long* stats, uint4* liveScratch, float4* escScratch, int variant, cudaStream_t stream) {
+                                 uint32_t* pathLength, unsigned long long* stats, float* accum, uint4* liveScratch, float4* escScratch, int variant,
+                                 cudaStream_t stream) {
   if (nItems == 0) return cudaSuccess;
   if (variant == 1 || !liveScratch || !escScratch) {
     const uint32_t blocks = (nItems + kTraceThreads - 1) / kTraceThreads;
     trace_wavefront_kernel_v1<<<blocks, kTraceThreads, 0, stream>>>(scene, s, pix, nItems, sampleBegin, samplesPerLaunch, qUv, qThrSlot,
-                                                                   qCount, sampleCount, pathLength, stats);
+                                                                   qCount, sampleCount, pathLength, stats, accum);
     return cudaGetLastError();
   }
   const uint32_t blocks = (nItems + kBlockItems - 1) / kBlockItems;
   const uint32_t p2w = variant >= 10 ? (uint32_t)(variant - 10) : (uint32_t)(kTraceThreads / 32);
   trace_wavefront_kernel<<<blocks, kTraceThreads, 0, stream>>>(scene, s, pix, nItems, sampleBegin, samplesPerLaunch, qUv, qThrSlot,
-                                                              qCount, sampleCount, pathLength, stats, liveScratch, escScratch, p2w);
+                                                              qCount, sampleCount, pathLength, stats, accum, liveScratch, escScratch, p2w);
   return cudaGetLastError();
 }
 
@@ -368,6 +380,7 @@ trace_items_kernel(const SceneSoA* __restrict__ scene, const DeviceSettings s, c
     const PathResult r = tracePath(cx, cy, s, sc, [&]() { return rng.uniformHalf(); });
     len = r.length;
     if (r.escaped) { esc = 1; escapedUv(r.dir, s.azimuth, u, v); thr = r.throughput; }
+    else if (r.emitted) { esc = 2; thr = r.throughput; }        // ended on an emitter: thr is the radiance itself
   }
   if (escaped) escaped[i] = esc;
   if (length) length[i] = len;
@@ -401,7 +414,7 @@ trace_fixed_kernel(const SceneSoA* __restrict__ scene, const DeviceSettings s, u
     if (next == perPath) next = 0;
     return v;
   });
-  escaped[i] = r.escaped ? 1 : 0;
+  escaped[i] = r.escaped ? 1 : (r.emitted ? 2 : 0);
   length[i] = r.length;
   const V3 d = r.escaped ? r.dir : v3(0.f, 0.f, 0.f);
   dir3[3 * i] = d.x; dir3[3 * i + 1] = d.y; dir3[3 * i + 2] = d.z;

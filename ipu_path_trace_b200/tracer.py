@@ -125,6 +125,22 @@ class PathTracer:
         self._check(self.lib.b200pt_set_render_settings(self.h, seed, aa_noise_scale, fov, az, samples_per_step),
                     "init_render_settings")
 
+    def set_scene(self, prims):
+        """Scene as data (b200pt_set_scene): list of dicts with shape ('sphere'|'disc'), bsdf ('diffuse'|'specular'|
+        'refractive'), centre, normal (disc), radius, colour, emission; None / [] restores the reference's built-in scene."""
+        shapes = {"sphere": 0, "disc": 1}
+        bsdfs = {"diffuse": 0, "specular": 1, "refractive": 2}
+        prims = list(prims or [])
+        arr = (_lib.Primitive * max(1, len(prims)))()
+        for i, p in enumerate(prims):
+            arr[i].shape = shapes[p["shape"]]; arr[i].material = bsdfs[p.get("bsdf", "diffuse")]
+            arr[i].centre = (C.c_float * 3)(*[float(x) for x in p["centre"]])
+            arr[i].normal = (C.c_float * 3)(*[float(x) for x in p.get("normal", (0, 1, 0))])
+            arr[i].radius = float(p["radius"])
+            arr[i].colour = (C.c_float * 3)(*[float(x) for x in p.get("colour", (1, 1, 1))])
+            arr[i].emission = (C.c_float * 3)(*[float(x) for x in p.get("emission", (0, 0, 0))])
+        self._check(self.lib.b200pt_set_scene(self.h, arr, len(prims)), "set_scene")
+
     def setup(self, worklist: np.ndarray):
         wl = np.ascontiguousarray(worklist, dtype=TRACE_RECORD)
         self._check(self.lib.b200pt_setup(self.h, _ptr(wl), len(wl)), "setup")

@@ -205,6 +205,13 @@ class Oracle:
         self.lib.orc_trace_philox(n, _ptr(items), C.c_uint32(sample), C.byref(cs), _ptr(esc), _ptr(uv), _ptr(t), _ptr(length), _ptr(cam))
         return esc, uv, t, length, cam
 
+    def set_scene(self, prims) -> None:
+        """Scene as data (the reference's comment at codelets.cpp:90-92): list of dicts with shape ('sphere'|'disc'),
+        bsdf ('diffuse'|'specular'|'refractive'), centre, normal (disc), radius, colour, emission. None / [] restores the
+        built-in scene."""
+        rows = scene_rows(prims)
+        self.lib.orc_set_scene(len(rows), _ptr(rows) if len(rows) else None)
+
     def philox(self, c, k) -> np.ndarray:
         out = np.zeros(4, np.uint32)
         self.lib.orc_philox(*[C.c_uint32(int(x)) for x in c], *[C.c_uint32(int(x)) for x in k], _ptr(out))
@@ -369,6 +376,33 @@ class Reference:
         stop = np.zeros(rnd.size, np.int32); w = np.zeros(rnd.size, np.float32)
         self.lib.ref_roulette(rnd.size, _ptr(rnd), C.c_float(stop_prob), _ptr(stop), _ptr(w))
         return stop, w
+
+
+def scene_rows(prims) -> np.ndarray:
+    """-> (n, 15) float32: shape, bsdf, centre[3], normal[3], radius, colour[3], emission[3]."""
+    shapes = {"sphere": 0, "disc": 1}
+    bsdfs = {"diffuse": 0, "specular": 1, "refractive": 2}
+    rows = np.zeros((len(prims or []), 15), np.float32)
+    for i, p in enumerate(prims or []):
+        rows[i, 0] = shapes[p["shape"]]; rows[i, 1] = bsdfs[p.get("bsdf", "diffuse")]
+        rows[i, 2:5] = p["centre"]; rows[i, 5:8] = p.get("normal", (0, 1, 0)); rows[i, 8] = p["radius"]
+        rows[i, 9:12] = p.get("colour", (1, 1, 1)); rows[i, 12:15] = p.get("emission", (0, 0, 0))
+    return rows
+
+
+def reference_scene(with_light: bool = False) -> list:
+    """The scene of codelets.cpp:110-144 as data; with_light adds the emitter the reference has commented out
+    (:117 Sphere(Vec(12, 8, -5.3), .3), :142 Object(zero colour, lightW = 10000, diffuse))."""
+    g = 2.0
+    s = [dict(shape="sphere", centre=(-1.8575, -0.98714, -3.6), radius=0.6, colour=(1 * g, .89 * g, .55 * g), bsdf="diffuse"),
+         dict(shape="sphere", centre=(0.74795, -0.55, -4.3816), radius=1.05, colour=(1, 1, 1), bsdf="specular"),
+         dict(shape="sphere", centre=(1.9929, -1.08666, -3.23), radius=0.5, colour=(.75, .75, .75), bsdf="refractive"),
+         dict(shape="sphere", centre=(-0.19931, -1.183, -2.75), radius=0.4, colour=(.8 * g, .06 * g, .391 * g), bsdf="diffuse"),
+         dict(shape="sphere", centre=(-0.19931, -1.183, -2.75), radius=0.4001, colour=(1, 1, 1), bsdf="refractive"),
+         dict(shape="disc", centre=(0, -1.6, -5.22), normal=(0, 1, 0), radius=3.5, colour=(.98 * g, .76 * g, .66 * g), bsdf="diffuse")]
+    if with_light:
+        s.insert(5, dict(shape="sphere", centre=(12, 8, -5.3), radius=0.3, colour=(0, 0, 0), emission=(10000, 10000, 10000), bsdf="diffuse"))
+    return s
 
 
 def make_worklist(width: int, height: int) -> np.ndarray:

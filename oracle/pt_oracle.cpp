@@ -53,19 +53,27 @@ struct Prim {
   float planeD;    // disc only: |centre . n|   (light.hpp:101, note the abs)
   V3 colour;
   int bsdf;
+  int emissive;    // light.hpp Material::emissive: emission != 0
+  V3 emission;
 };
 
 // codelets.cpp:110-144. Colours carry the 2x gain (:127-130). No emitters (:117,142).
 static const int kNumPrims = 6;
 static Prim makeSphere(float cx, float cy, float cz, float r, V3 colour, int bsdf) {
   Prim p; p.shape = SPHERE; p.centre = v3(cx, cy, cz); p.normal = v3(0.f, 1.f, 0.f);
-  p.radius2 = r * r; p.planeD = 0.f; p.colour = colour; p.bsdf = bsdf; return p;
+  p.radius2 = r * r; p.planeD = 0.f; p.colour = colour; p.bsdf = bsdf; p.emissive = 0; p.emission = v3(0.f, 0.f, 0.f); return p;
 }
 static Prim makeDisc(V3 n, V3 c, float r, V3 colour, int bsdf) {
   Prim p; p.shape = DISC; p.centre = c; p.normal = unit(n);
-  p.radius2 = r * r; p.planeD = std::abs(dot(c, p.normal)); p.colour = colour; p.bsdf = bsdf; return p;
+  p.radius2 = r * r; p.planeD = std::abs(dot(c, p.normal)); p.colour = colour; p.bsdf = bsdf; p.emissive = 0; p.emission = v3(0.f, 0.f, 0.f); return p;
 }
-static const Prim* sceneTable() {
+// The reference anticipates passing the scene as data (codelets.cpp:90-92 "currently hard coded"); orc_set_scene
+// replaces the built-in table (the product's counterpart is b200pt_set_scene). Not thread-safe: set it between calls.
+static std::vector<Prim> g_userScene;
+static const Prim* builtinScene();
+static const Prim* sceneTable() { return g_userScene.empty() ? builtinScene() : g_userScene.data(); }
+static int sceneCount() { return g_userScene.empty() ? kNumPrims : (int)g_userScene.size(); }
+static const Prim* builtinScene() {
   static Prim prims[kNumPrims];
   static bool built = false;
   if (!built) {
@@ -116,7 +124,8 @@ static int closestHit(V3& o, V3 d, V3& normalOut) {
   const Prim* prims = sceneTable();
   int best = -1;
   float bestT = std::numeric_limits<float>::infinity();
-  for (int i = 0; i < kNumPrims; ++i) {
+  const int count = sceneCount();
+  for (int i = 0; i < count; ++i) {
     const float t = prims[i].shape == SPHERE ? hitSphere(prims[i], o, d) : hitDisc(prims[i], o, d);
     if (t > kHitEps && t < bestT) { bestT = t; best = i; }
   }
@@ -206,6 +215,11 @@ static int tracePathRecords(float camX, float camY, const Settings& s, Draw&& dr
       break;
     }
     const Prim& p = prims[hit];
+    if (p.emissive) {                       // codelets.cpp:192-196
+      putRecord(rec[count++], p.emission, rr, C_EMIT);
+      lit = true;
+      break;
+    }
     if (p.bsdf == DIFFUSE) {
       const float u1 = draw();
       const float u2 = draw();
@@ -413,7 +427,27 @@ void orc_trace_philox(int n, const TraceRec* items, std::uint32_t sample, const 
       rec[cnt - 1].clr[0] = rec[cnt - 1].clr[1] = rec[cnt - 1].clr[2] = 1.f;
       const V3 t = walkBack(rec, cnt);
       throughput3[3 * i] = t.x; throughput3[3 * i + 1] = t.y; throughput3[3 * i + 2] = t.z;
+    } else if (rec[cnt - 1].type == C_EMIT) {
+      // the path ended on an emitter: escaped = 2, throughput3 = the radiance the backward walk yields (no NIF lookup)
+      escaped[i] = 2;
+      const V3 t = walkBack(rec, cnt);
+      throughput3[3 * i] = t.x; throughput3[3 * i + 1] = t.y; throughput3[3 * i + 2] = t.z;
     }
+  }
+}
+
+// Scene as data: n primitives {shape (0 sphere, 1 disc), bsdf (0 diffuse, 1 specular, 2 refractive), centre[3], normal[3]
+// (disc; normalised here like light::Disc's constructor), radius, colour[3], emission[3]} as 15 floats each, emissive iff
+// any emission component is non-zero (light.hpp Material). n = 0 restores the built-in scene of codelets.cpp:110-144.
+void orc_set_scene(int n, const float* prims15) {
+  g_userScene.clear();
+  for (int i = 0; i < n; ++i) {
+    const float* a = prims15 + 15 * (std::size_t)i;
+    const V3 c = v3(a[2], a[3], a[4]), nn = v3(a[5], a[6], a[7]), col = v3(a[9], a[10], a[11]), em = v3(a[12], a[13], a[14]);
+    Prim p = (int)a[0] == SPHERE ? makeSphere(c.x, c.y, c.z, a[8], col, (int)a[1]) : makeDisc(nn, c, a[8], col, (int)a[1]);
+    p.emissive = (em.x != 0.f || em.y != 0.f || em.z != 0.f) ? 1 : 0;
+    p.emission = em;
+    g_userScene.push_back(p);
   }
 }
 

@@ -42,7 +42,7 @@ long long orc_render(int n, TraceRec* items, std::uint32_t sampleBegin, std::uin
     // compact the escaped rays (the reference evaluates the NIF for every path, escaped or
     // not, and discards the rest: codelets.cpp:348-352; the result is the same)
     qu.clear(); qv.clear(); qidx.clear();
-    for (int i = 0; i < n; ++i) if (escaped[i]) { qidx.push_back(i); qu.push_back(uv[2 * i]); qv.push_back(uv[2 * i + 1]); }
+    for (int i = 0; i < n; ++i) if (escaped[i] == 1) { qidx.push_back(i); qu.push_back(uv[2 * i]); qv.push_back(uv[2 * i + 1]); }
     double t1 = omp_get_wtime();
     bgr.resize(3 * qidx.size());
     if (!qidx.empty()) orc_nif_forward(nif, (int)qidx.size(), qu.data(), qv.data(), nifMode, bgr.data());
@@ -56,6 +56,9 @@ long long orc_render(int n, TraceRec* items, std::uint32_t sampleBegin, std::uin
     }
     for (int i = 0; i < n; ++i) {
       if (items[i].u >= s->width || items[i].v >= s->height) continue;
+      if (escaped[i] == 2) {           // ended on an emitter (codelets.cpp:192-196, :255-298): radiance without a NIF lookup
+        items[i].r += thr[3 * i]; items[i].g += thr[3 * i + 1]; items[i].b += thr[3 * i + 2];
+      }
       items[i].pathLength = (std::uint16_t)(items[i].pathLength + length[i]);
       items[i].sampleCount = (std::uint16_t)(items[i].sampleCount + 1);
     }
