@@ -50,9 +50,9 @@ def measured_peaks():
 
 def nif_traffic_bytes():
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE nif_tc_kernel launch of this very workload
-    (one wavefront of C2), from the committed `ncu --set full` capture (profiles/r1_nif_tc_traffic.json);
+    (one wavefront of C2), from the committed `ncu --set full` capture (profiles/r2_nif_tc_traffic.json);
     None when no capture has been committed."""
-    p = os.path.join(ROOT, "profiles", "r1_nif_tc_traffic.json")
+    p = os.path.join(ROOT, "profiles", "r2_nif_tc_traffic.json")
     if not os.path.exists(p):
         return None
     d = json.load(open(p))
