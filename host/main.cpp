@@ -10,6 +10,8 @@
 #include "logging.hpp"
 
 int main(int argc, char** argv) {
+  // Load every kernel when the contexts are created (device acquisition), not inside the first render step.
+  setenv("CUDA_MODULE_LOADING", "EAGER", 0);
   try {
     Options opts;
     try {
