@@ -199,3 +199,35 @@ def test_cli_load_balancing_really_redeals(cli, lib_built, nif_model, O, orc, tm
     exr = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED).astype(np.float64)
     want = _oracle_film(O, orc, lib_built, nif_model, w, h, spp)
     assert _rrmse(exr, want) < 0.01
+
+
+@pytest.mark.parametrize("film", ["--host-film", "device"])
+def test_cli_survives_a_client_that_drops_the_socket_mid_render(cli, nif_model, tmp_path, film):
+    """the async host task may be inside startSendingRawImage when the link dies. A client connects, takes the
+    first raw image and then closes the socket without `detach` or `stop`, in the middle of the save intervals; the render
+    must carry on head-less to the end, write its files and exit 0 (PathTracerApp.cpp:543-546: "If the Remote-UI detaches
+    just continue rendering")."""
+    import cv2
+    from ui_client import UiClient
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    w, h = 128, 96
+    assets = _assets(tmp_path, nif_model)
+    port = _free_port()
+    out = str(tmp_path / "drop.png")
+    cmd = [cli, "--assets", assets, "-w", str(w), "-h", str(h), "-s", "4096", "--samples-per-step", "16", "--save-interval", "2", "-o", out,
+           "--ui-port", str(port), "--ui-accept-timeout", "120"] + ([film] if film.startswith("--") else [])
+    p = subprocess.Popen(cmd, stderr=subprocess.PIPE, text=True)
+    try:
+        c = UiClient(port, connect_timeout=120)
+        assert c.wait(lambda c: len(c.images) >= 1 and len(c.progress) >= 4, timeout=120)
+        c.close()                                               # hang up, no good-bye
+        rc = p.wait(timeout=180)
+        err = p.stderr.read()
+        assert rc == 0, err[-2000:]
+        assert "Remote UI connection lost" in err or "Remote UI disconnected" in err
+        assert "Render finished" in err and "Saved images at step 256" in err
+        exr = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED)
+        assert exr is not None and exr.shape == (h, w, 3) and np.isfinite(exr).all() and exr.mean() > 0
+    finally:
+        if p.poll() is None:
+            p.kill()

@@ -171,3 +171,27 @@ def test_setup_next_and_pinned_buffers_equal_the_serial_programs(lib_built, nif_
         assert np.array_equal(x["pathLength"], y["pathLength"]) and np.array_equal(x["sampleCount"], y["sampleCount"])
         np.testing.assert_allclose(_rgb(x), _rgb(y), rtol=1e-5, atol=1e-6)
     assert not np.array_equal(a[0]["v"], a[1]["v"])
+
+
+def test_c5_size_properties(lib_built, nif_model):
+    """BASELINE config C5's image (3840x2160 = 8.3 M work items, the largest single-GPU work list): counts, escape
+    statistics, finiteness, and the film of one step equals the records (size-independent properties; the oracle needs
+    minutes at this size)."""
+    W, H, sps = 3840, 2160, 2
+    t = lib_built.PathTracer(W, H)
+    t.init_nif_weights(nif_model)
+    t.init_render_settings(samples_per_step=sps)
+    t.setup(lib_built.create_work_list_for_image(W, H))
+    t.path_trace()
+    out, ctr = t.read_results()
+    assert ctr.paths == W * H * sps
+    assert 0.96 < ctr.escaped / ctr.paths < 0.985
+    assert np.all(out["sampleCount"] == sps) and int(out["pathLength"].sum()) == ctr.path_segments
+    rgb = _rgb(out)
+    assert np.all(np.isfinite(rgb)) and rgb.min() >= 0
+    t.film_accumulate()
+    film = t.film_read(1.0)
+    want = np.zeros((H, W, 3), np.float32)
+    want[out["v"], out["u"]] = np.stack([out["b"], out["g"], out["r"]], 1) / np.float32(sps)
+    np.testing.assert_allclose(film, want, rtol=1e-6, atol=1e-8)
+    t.close()
