@@ -214,7 +214,8 @@ def test_cli_survives_a_client_that_drops_the_socket_mid_render(cli, nif_model, 
     assets = _assets(tmp_path, nif_model)
     port = _free_port()
     out = str(tmp_path / "drop.png")
-    cmd = [cli, "--assets", assets, "-w", str(w), "-h", str(h), "-s", "4096", "--samples-per-step", "16", "--save-interval", "2", "-o", out,
+    # 4096 steps of 64 samples (~5 s): the render must still be running when the client has its first image and hangs up
+    cmd = [cli, "--assets", assets, "-w", str(w), "-h", str(h), "-s", "262144", "--samples-per-step", "64", "--save-interval", "32", "-o", out,
            "--ui-port", str(port), "--ui-accept-timeout", "120"] + ([film] if film.startswith("--") else [])
     p = subprocess.Popen(cmd, stderr=subprocess.PIPE, text=True)
     try:
@@ -225,7 +226,7 @@ def test_cli_survives_a_client_that_drops_the_socket_mid_render(cli, nif_model, 
         err = p.stderr.read()
         assert rc == 0, err[-2000:]
         assert "Remote UI connection lost" in err or "Remote UI disconnected" in err
-        assert "Render finished" in err and "Saved images at step 256" in err
+        assert "Render finished" in err and "Saved images at step 4096" in err
         exr = cv2.imread(out[:-4] + ".exr", cv2.IMREAD_UNCHANGED)
         assert exr is not None and exr.shape == (h, w, 3) and np.isfinite(exr).all() and exr.mean() > 0
     finally:
