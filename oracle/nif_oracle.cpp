@@ -140,6 +140,15 @@ int orc_nif_forward(const Nif* nif, int n, const float* u, const float* v, int m
   return 0;
 }
 
+// The decode alone (NifModel.cpp:226-242; host twin :492-509): x * max + mean (eps already folded into mean), optional exp.
+void orc_nif_decode(int n, const float* x3, float maxv, const float* mean3, int logToneMap, float* out3) {
+  for (int i = 0; i < n; ++i)
+    for (int c = 0; c < 3; ++c) {
+      const float o = x3[3 * i + c] * maxv + mean3[c];
+      out3[3 * i + c] = logToneMap ? expf(o) : o;
+    }
+}
+
 // Σ (2·in·out + out) — the reference's own FLOP count (NifModel.cpp:122-134)
 long long orc_nif_flops_per_eval(const Nif* nif) {
   long long f = 0;

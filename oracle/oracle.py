@@ -252,6 +252,13 @@ class Oracle:
         assert rc == 0
         return out
 
+    def nif_decode(self, x3, maxv: float, mean3, log_tone_map: bool) -> np.ndarray:
+        x3 = np.ascontiguousarray(x3, dtype=np.float32)
+        out = np.zeros_like(x3)
+        mean = np.ascontiguousarray(mean3, dtype=np.float32)
+        self.lib.orc_nif_decode(x3.shape[0], _ptr(x3), C.c_float(maxv), _ptr(mean), int(bool(log_tone_map)), _ptr(out))
+        return out
+
     def nif_flops_per_eval(self, nif: NifLayers) -> int:
         cn, keep = nif.to_c()
         return int(self.lib.orc_nif_flops_per_eval(C.byref(cn)))
@@ -412,6 +419,35 @@ def make_worklist(width: int, height: int) -> np.ndarray:
     items["u"] = uu
     items["v"] = vv
     return items
+
+
+class NifTwinsReference:
+    """The reference's host-side twins of the NIF's two ends - NifModel::generateInputSamples / makeCoefficients /
+    makeGridCoordsUV and NifModel::decodeSamples (src/neural_networks/NifModel.cpp:403-443,466-509) - cut out of the
+    reference source at build time and compiled unmodified (oracle/_ref/libref_niftwins.so). TEST INFRASTRUCTURE ONLY."""
+
+    PATH = os.path.join(HERE, "_ref", "libref_niftwins.so")
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(NifTwinsReference.PATH)
+
+    def __init__(self):
+        self.lib = C.CDLL(self.PATH)
+
+    def encode_grid(self, height: int, width: int, embedding_dim: int):
+        n = height * width
+        f = np.zeros((n, 4 * embedding_dim), np.float32)
+        u = np.zeros(n, np.float32); v = np.zeros(n, np.float32)
+        assert self.lib.refnif_encode_grid(height, width, embedding_dim, _ptr(f), _ptr(u), _ptr(v)) == 0
+        return f, u, v
+
+    def decode(self, x3, maxv: float, mean3, eps: float, log_tone_map: bool) -> np.ndarray:
+        x3 = np.ascontiguousarray(x3, dtype=np.float32)
+        out = np.zeros_like(x3)
+        mean = np.ascontiguousarray(mean3, dtype=np.float32)
+        assert self.lib.refnif_decode(x3.shape[0], _ptr(x3), C.c_float(maxv), _ptr(mean), C.c_float(eps), int(bool(log_tone_map)), _ptr(out)) == 0
+        return out
 
 
 class CornellReference:
