@@ -217,13 +217,15 @@ def test_cli_survives_a_client_that_drops_the_socket_mid_render(cli, nif_model, 
     # 4096 steps of 64 samples (~5 s): the render must still be running when the client has its first image and hangs up
     cmd = [cli, "--assets", assets, "-w", str(w), "-h", str(h), "-s", "262144", "--samples-per-step", "64", "--save-interval", "32", "-o", out,
            "--ui-port", str(port), "--ui-accept-timeout", "120"] + ([film] if film.startswith("--") else [])
-    p = subprocess.Popen(cmd, stderr=subprocess.PIPE, text=True)
+    log = open(tmp_path / "stderr.log", "w")                    # 4096 log lines: a pipe nobody drains would fill up and block the render
+    p = subprocess.Popen(cmd, stderr=log, text=True)
     try:
         c = UiClient(port, connect_timeout=120)
         assert c.wait(lambda c: len(c.images) >= 1 and len(c.progress) >= 4, timeout=120)
         c.close()                                               # hang up, no good-bye
         rc = p.wait(timeout=180)
-        err = p.stderr.read()
+        log.close()
+        err = open(tmp_path / "stderr.log").read()
         assert rc == 0, err[-2000:]
         assert "Remote UI connection lost" in err or "Remote UI disconnected" in err
         assert "Render finished" in err and "Saved images at step 4096" in err
