@@ -201,11 +201,17 @@ __device__ __forceinline__ uint32_t umInstr(uint32_t n8) { return (1u << 4) | (n
 // Optional in-kernel timers (build with -DB200PT_PROFILE; scratch/nif_prof.py reads them).
 #ifdef B200PT_PROFILE
 __device__ unsigned long long g_tcProf[148 * 16];
+// Timeline of ONE tile (CTA 0, tile iteration kTraceIt): [chunk * 4 + {0 loop top, 1 barriers passed, 2 turn taken, 3 issued}] for the MMA
+// warps, [128 + job * 2 + {0 accumulator full seen, 1 hand-over arrives done}] for epilogue warp 0; scratch/nif_timeline.py prints it.
+__device__ unsigned long long g_tcTrace[256];
+constexpr unsigned kTraceIt = 8;
+#define PROF_MARK(cond, idx) do { if ((cond) && blockIdx.x == 0) g_tcTrace[(idx)] = clock64(); } while (0)
 #define PROF_T() clock64()
 #define PROF_ADD(var, t0) (var) += clock64() - (t0)
 #else
 #define PROF_T() 0ll
 #define PROF_ADD(var, t0) ((void)(var), (void)(t0))
+#define PROF_MARK(cond, idx) ((void)0)
 #endif
 
 struct TcSmem {
@@ -410,6 +416,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
           continue;
         }
+        PROF_MARK(it == kTraceIt && lane == 0, c * 4 + 0);
         const bool isOut = (flags & kChOut) != 0;
         // the two half-jobs of a layer accumulate concurrently (K order above): the accumulator slot
         // and how often the slot was used before in this tile come precomputed with the chunk
@@ -430,6 +437,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           if (CG == 2) mbarWait<CG>(bar(BAR_PEER_W_FULL + stage), phase);
           PROF_ADD(pPeer, t1); }
         tcFenceAfter();
+        PROF_MARK(it == kTraceIt && lane == 0, c * 4 + 1);
         const uint32_t dT = tmemBase + (isOut ? outCol : accCol0 + buf * (uint32_t)NH);
         const uint32_t bRows = n8 * (8u / CG);                                        // rows of B this CTA holds
         uint32_t aLo = (((flags & kChSrcFeat) ? featLo : actLo) + ch.aOff16) | ((2048u >> 4) << 16);
@@ -457,6 +465,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           PROF_ADD(pPeer, t0);
         }
         const long long tIssue = PROF_T();
+        PROF_MARK(it == kTraceIt && lane == 0, c * 4 + 2);
         // Two separate loops: a predicated-off twin UTCHMMA still occupies a tensor-queue slot.
         if (aFromTmem) {
 #pragma unroll
@@ -487,6 +496,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           if (leader) asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(turnAddr), "r"(g + 1u) : "memory");
         }
         PROF_ADD(pIssue, tIssue);
+        PROF_MARK(it == kTraceIt && lane == 0, c * 4 + 3);
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -562,6 +572,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           const uint32_t jobInTile = 2u * (uint32_t)l + h;
           const uint32_t buf = jobInTile % kSlots, accPhase = (it * m.slotUses[buf] + jobInTile / kSlots) & 1u;
           { const long long t0 = PROF_T(); mbarWait<CG>(bar(BAR_ACC_FULL + buf), accPhase); PROF_ADD(eWait, t0); }
+          PROF_MARK(it == kTraceIt && ew == 0 && lane == 0, 128 + jobInTile * 2);
           const long long tw = PROF_T();
           tcFenceAfter();
           const uint32_t tBase = laneBase + accCol0 + buf * (uint32_t)NH + colHalf * colsMine;
@@ -623,6 +634,7 @@ nif_tc_kernel(const __grid_constant__ NifTcModel m, const NifIo io) {
           tcFenceBefore();            // my TMEM accesses are ordered before the arrives below
           __syncwarp();
           if (lane == 0) { arriveIssuer(BAR_ACC_EMPTY + buf); arriveIssuer(BAR_ACT_READY + h); }
+          PROF_MARK(it == kTraceIt && ew == 0 && lane == 0, 128 + jobInTile * 2 + 1);
           PROF_ADD(eWork, tw);
         }
       }
@@ -692,6 +704,9 @@ cudaError_t prepareNifTc(const NifTcModel& m) {
 #ifdef B200PT_PROFILE
 extern "C" int b200pt_debug_tc_profile(unsigned long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, g_tcProf, sizeof(unsigned long long) * n);
+}
+extern "C" int b200pt_debug_tc_trace(unsigned long long* out, int n) {
+  return (int)cudaMemcpyFromSymbol(out, g_tcTrace, sizeof(unsigned long long) * n);
 }
 #endif
 
