@@ -169,7 +169,7 @@ def run_reference(args) -> None:
         return
     vals = []
     desc, cores = "", 1
-    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    per_step = args.cpu_seconds if args.cpu_seconds > 0 else max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     for i in range(args.warmup + args.steps):
         v, desc, cores = cpu_sample_run(per_step)
         if i >= args.warmup:
@@ -458,6 +458,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--samples-per-step", type=int, default=SAMPLES_PER_STEP)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=0.0, help="--impl reference: seconds of CPU work per step (default: sized so the run takes ~2 minutes)")
     ap.add_argument("--no-extras", action="store_true", help="skip the C4 microbenchmark and the C++ host runs (config.c4 / cli_c2 / cli_c5)")
     ap.add_argument("--cli-spp", type=int, default=100000, help="samples per pixel of the C++ host run (README.md:82 uses 100000)")
     args = ap.parse_args()
