@@ -315,6 +315,18 @@ RenderSummary PathTracerApp::execute() {
   nvtxRangePop();
   logging::info("Created worklists for {} GPUs ({} work items each)", jobs.size(), jobs.front().size());
   LoadBalancer work(jobs);
+  // Record-stream modes move both work lists over the host link every step: page-lock them (the copies of setup /
+  // read_results then run at the full link rate). Declared after `work` so that it unregisters before the lists are freed.
+  struct ListPin {
+    std::vector<void*> p;
+    ~ListPin() { for (auto* q : p) cudaHostUnregister(q); }
+  } listPin;
+  if (recordStream) {
+    for (RecordList* l : {&work.getWork().active(), &work.getWork().inactive()}) {
+      if (cudaHostRegister(l->data(), l->size() * sizeof(TraceRecord), cudaHostRegisterPortable) == cudaSuccess) listPin.p.push_back(l->data());
+      else cudaGetLastError();
+    }
+  }
 
   // Setup remote user interface (:618-633). Unlike the reference the state a client has not touched
   // yet starts from the command line, with or without a client.
