@@ -260,6 +260,28 @@ int b200pt_cornell_trace_paths(const b200pt_cornell_config* cfg, size_t n, const
                                float* rgb, uint32_t* depth);
 const char* b200pt_cornell_last_error(void);
 
+/* No counterpart in the reference: its renderer is a CPU program and owns its heap. This entry point exists for callers that are
+ * not in a position to ask the CUDA driver for memory while they render: a plug-in that was handed one output buffer by its
+ * host application and a fixed share of the GPU's memory besides, a frame loop that cannot afford cudaMalloc's device-wide
+ * synchronisation, a process running beside an allocator that has already claimed the whole device. It renders what
+ * b200pt_cornell_render renders with rng_mode = B200PT_CORNELL_TILE_STREAMS (any other rng_mode is rejected), same bits, but
+ *   - the image goes to rgb_device, a DEVICE buffer of height x width x 3 fp32 that the caller owns and that lives on
+ *     cfg->device; it is cleared and then written, and is complete when the call returns (the call is synchronous);
+ *   - the kernel's working memory (the per-tile generator states and the two statistics counters) lives in an array that is
+ *     part of the library image: 256 B + 16 B per tile, sized for B200PT_CORNELL_NOALLOC_MAX_TILES tiles (about 256 KiB).
+ *     Every GPU on which this process uses the library keeps that array until the process exits;
+ *   - ceil(width / tile_width) * ceil(height / tile_height) above that limit fails with B200PT_ERR_INVALID and a message that
+ *     names both numbers; nothing is rendered;
+ *   - neither cudaMalloc / cudaFree nor any other allocating call is made, on the device or on the host heap. That is also why
+ *     stats->device_ms comes back as 0: timing needs events, and creating events allocates.
+ * The first call on each device looks up the array's device address (and, like any first CUDA call, brings up the context and
+ * loads the kernels). Make that first call before you begin capturing a stream. The array is shared by all calls on a device
+ * and still holds what the previous call left in it; the function rewrites the parts it reads, so two calls in a row are
+ * independent, but two calls that run on the same GPU at the same time (two host threads, same cfg->device) overwrite each
+ * other's generator states and counters. Serialise them yourself. */
+enum { B200PT_CORNELL_NOALLOC_MAX_TILES = 16384 };
+int b200pt_cornell_render_noalloc(const b200pt_cornell_config* cfg, void* rgb_device, b200pt_cornell_stats* stats);
+
 #ifdef __cplusplus
 }
 #endif

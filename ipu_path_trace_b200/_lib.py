@@ -18,7 +18,7 @@ EXPORTS = [
     "b200pt_film_read_device", "b200pt_film_tonemap", "b200pt_set_sample_index", "b200pt_get_counters",
     "b200pt_nif_flops_per_eval", "b200pt_nif_infer", "b200pt_nif_infer_device", "b200pt_trace_wavefront",
     "b200pt_trace_fixed", "b200pt_kat",
-    "b200pt_cornell_render", "b200pt_cornell_trace_paths", "b200pt_cornell_last_error",
+    "b200pt_cornell_render", "b200pt_cornell_trace_paths", "b200pt_cornell_last_error", "b200pt_cornell_render_noalloc",
 ]
 
 
@@ -121,5 +121,6 @@ def load() -> C.CDLL:
     lib.b200pt_cornell_render.argtypes = [C.POINTER(CornellConfig), vp, C.POINTER(CornellStats)]
     lib.b200pt_cornell_trace_paths.argtypes = [C.POINTER(CornellConfig), sz, vp, vp, vp, vp]
     lib.b200pt_cornell_last_error.restype = C.c_char_p
+    lib.b200pt_cornell_render_noalloc.argtypes = [C.POINTER(CornellConfig), vp, C.POINTER(CornellStats)]
     _lib = lib
     return lib

@@ -51,6 +51,21 @@ def render(opts: CornellOptions):
     return rgb, {"total_ray_casts": int(stats.total_ray_casts), "max_path_length": int(stats.max_path_length), "device_ms": float(stats.device_ms)}
 
 
+NOALLOC_MAX_TILES = 16384          # B200PT_CORNELL_NOALLOC_MAX_TILES
+
+
+def render_noalloc(opts: CornellOptions, rgb_device_ptr: int):
+    """b200pt_cornell_render_noalloc: the TILE_STREAMS render for callers that may not allocate GPU memory while rendering
+    (a plug-in on a fixed memory share, a frame loop that avoids cudaMalloc's device-wide sync). The image is written to the
+    caller's DEVICE buffer at `rgb_device_ptr` (height x width x 3 float32 on opts.device); the kernel's working memory is an
+    array built into the library, good for NOALLOC_MAX_TILES tiles. Calls on one device must not overlap. -> stats dict."""
+    lib = _lib.load()
+    stats = _lib.CornellStats()
+    cfg = opts.to_c()
+    _check(lib, lib.b200pt_cornell_render_noalloc(C.byref(cfg), C.c_void_p(rgb_device_ptr), C.byref(stats)), "b200pt_cornell_render_noalloc")
+    return {"total_ray_casts": int(stats.total_ray_casts), "max_path_length": int(stats.max_path_length), "device_ms": float(stats.device_ms)}
+
+
 def trace_paths(opts: CornellOptions, cam_xy: np.ndarray, rng_state: np.ndarray):
     """cam_xy (n,2) float32, rng_state (n,2) uint64 -> (rgb (n,3), depth (n,), advanced state (n,2))."""
     lib = _lib.load()

@@ -13,7 +13,9 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -539,3 +541,110 @@ done:
 }
 
 } // extern "C"
+
+// ---- b200pt_cornell_render_noalloc: the tile-stream render without a single allocation -------------------------
+//
+// For callers that cannot call cudaMalloc while they render (see include/b200pt.h: a plug-in living on a buffer and a memory
+// share given to it, a frame loop that must not take cudaMalloc's device-wide synchronisation, a neighbour allocator that
+// owns the rest of the GPU). cornell_tiles_kernel needs working memory that is neither input nor output: one xoroshiro128**
+// state per tile job and the two statistics counters. b200pt_cornell_render gets it from cudaMalloc; here it is this array,
+// which is part of the library's device image, so every device that loads the library has its own copy for as long as the
+// process lives. Layout: bytes [0,16) the counters (ray casts, longest path), bytes [256, 256 + 16 * tiles) the states.
+//
+// In host code the name gCornellScratch is only a handle for the symbol, not an address a kernel could use: the per-device
+// address comes from cudaGetSymbolAddress, asked once per device with that device current, and it is that pointer the
+// kernel receives.
+static __device__ __align__(256) unsigned char gCornellScratch[256 + (size_t)B200PT_CORNELL_NOALLOC_MAX_TILES * 2 * sizeof(uint64_t)];
+
+namespace {
+
+constexpr int kScratchMaxDevices = 64;
+constexpr size_t kScratchStatesOffset = 256;
+std::mutex g_scratchMutex;                                  // guards the table below, not the array's contents
+unsigned char* g_scratchAddress[kScratchMaxDevices] = {};
+
+// Device address of gCornellScratch on `device`, which must be the current device (cornellPrepare has selected it).
+int cornellScratchAddress(int device, unsigned char** out) {
+  if (device < 0 || device >= kScratchMaxDevices) return cornellFail(B200PT_ERR_INVALID, "device ordinal beyond the scratch table (64 devices)");
+  std::lock_guard<std::mutex> lock(g_scratchMutex);
+  if (!g_scratchAddress[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, gCornellScratch);
+    if (e != cudaSuccess || !p) return cornellFail(B200PT_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch array): ") + cudaGetErrorString(e));
+    g_scratchAddress[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_scratchAddress[device];
+  return B200PT_OK;
+}
+
+} // namespace
+
+extern "C" int b200pt_cornell_render_noalloc(const b200pt_cornell_config* cfg, void* rgbDevice, b200pt_cornell_stats* stats) {
+  DeviceGuard guard;
+  CornellParams p;
+  int rc = cornellPrepare(cfg, p);                          // validates cfg, selects cfg->device, uploads the scene constants
+  if (rc != B200PT_OK) return rc;
+  if (cfg->rng_mode != B200PT_CORNELL_TILE_STREAMS)
+    return cornellFail(B200PT_ERR_INVALID, "b200pt_cornell_render_noalloc renders rng_mode = B200PT_CORNELL_TILE_STREAMS only");
+  const uint64_t jobs = (uint64_t)p.tilesX * p.tilesY;
+  if (jobs > (uint64_t)B200PT_CORNELL_NOALLOC_MAX_TILES) {
+    char msg[200];
+    snprintf(msg, sizeof(msg), "%llu tiles exceed the %d tiles the built-in scratch array holds (B200PT_CORNELL_NOALLOC_MAX_TILES): use larger tiles or b200pt_cornell_render",
+             (unsigned long long)jobs, (int)B200PT_CORNELL_NOALLOC_MAX_TILES);
+    return cornellFail(B200PT_ERR_INVALID, msg);
+  }
+  if (!rgbDevice) return cornellFail(B200PT_ERR_INVALID, "null image buffer");
+  {
+    cudaPointerAttributes attr{};
+    const cudaError_t e = cudaPointerGetAttributes(&attr, rgbDevice);
+    if (e != cudaSuccess) { cudaGetLastError(); return cornellFail(B200PT_ERR_INVALID, std::string("rgb_device is not a CUDA pointer: ") + cudaGetErrorString(e)); }
+    if (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged)
+      return cornellFail(B200PT_ERR_INVALID, "rgb_device must be device memory (a host pointer was passed; b200pt_cornell_render takes host buffers)");
+    if (attr.type == cudaMemoryTypeDevice && attr.device != cfg->device)
+      return cornellFail(B200PT_ERR_INVALID, "rgb_device lives on another device than cfg->device");
+  }
+  unsigned char* scratch = nullptr;
+  rc = cornellScratchAddress(cfg->device, &scratch);
+  if (rc != B200PT_OK) return rc;
+  unsigned long long* dStats = reinterpret_cast<unsigned long long*>(scratch);
+  uint64_t* dJobs = reinterpret_cast<uint64_t*>(scratch + kScratchStatesOffset);
+  float* dFilm = static_cast<float*>(rgbDevice);
+  const size_t floats = (size_t)p.width * p.height * 3;
+  unsigned long long hStats[2] = {0, 0};
+
+  // The array still holds the previous call's counters and states. The counters are accumulated with atomics and the film
+  // with +=, so both must start at zero; the states of the tiles this call uses are all rewritten below.
+  CORNELL_CUDA(cudaMemset(dStats, 0, sizeof(hStats)));
+  CORNELL_CUDA(cudaMemset(dFilm, 0, floats * sizeof(float)));
+  {
+    // createTracingJobs (jobs.hpp:66-90) like b200pt_cornell_render, but generated in stack-sized pieces so that the host
+    // heap is not touched either: one stream per tile, 2^64 draws apart (xoshiro.hpp:43-58 jump).
+    constexpr size_t kPiece = 512;
+    uint64_t piece[kPiece * 2];
+    Xo s;
+    s.s0 = splitmix64(cfg->seed);
+    s.s1 = splitmix64(s.s0);
+    for (uint64_t j0 = 0; j0 < jobs; j0 += kPiece) {
+      const size_t count = (size_t)std::min<uint64_t>(kPiece, jobs - j0);
+      for (size_t j = 0; j < count; ++j) {
+        piece[2 * j] = s.s0; piece[2 * j + 1] = s.s1;
+        static const uint64_t kJump[2] = {0xdf900294d8f554a5ull, 0x170865df4b3201fcull};
+        uint64_t a = 0, b = 0;
+        for (int w = 0; w < 2; ++w)
+          for (int bit = 0; bit < 64; ++bit) {
+            if (kJump[w] & (1ull << bit)) { a ^= s.s0; b ^= s.s1; }
+            xoNext(s);
+          }
+        s.s0 = a; s.s1 = b;
+      }
+      // pageable source: the copy has left `piece` when cudaMemcpy returns, so the buffer can be refilled
+      CORNELL_CUDA(cudaMemcpy(dJobs + 2 * j0, piece, count * 2 * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    }
+  }
+  cornell_tiles_kernel<<<(unsigned)((jobs + 31) / 32), 32>>>(dJobs, dFilm, dStats, p);
+  CORNELL_CUDA(cudaGetLastError());
+  CORNELL_CUDA(cudaMemcpy(hStats, dStats, sizeof(hStats), cudaMemcpyDeviceToHost));     // waits for the kernel: the image is complete
+  if (stats) { stats->total_ray_casts = hStats[0]; stats->max_path_length = hStats[1]; stats->device_ms = 0.0; }
+done:
+  return rc;
+}
