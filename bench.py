@@ -242,8 +242,11 @@ def run_cli(n_gpus: int, width: int, height: int, spp: int, sps: int, save_inter
         out = os.path.join(tmp, f"{tag}.png")
         cmd = [exe, "-o", out, "--assets", assets, "-w", str(width), "-h", str(height), "-s", str(spp), "--samples-per-step", str(sps),
                "--ipus", str(n_gpus), "--save-interval", str(save_interval)]
+        # torch.distributed.run exports OMP_NUM_THREADS=1 to its ranks; the C++ host is its own program with a parallel
+        # PNG / EXR encoder and must see the machine as a user's shell would give it.
+        env = {k: v for k, v in os.environ.items() if k not in ("OMP_NUM_THREADS", "MKL_NUM_THREADS")}
         t0 = time.perf_counter()
-        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
         wall = time.perf_counter() - t0
         log = r.stderr
         if os.environ.get("B200PT_BENCH_LOGDIR"):

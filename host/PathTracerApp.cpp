@@ -5,6 +5,7 @@
 
 #include <nvtx3/nvToolsExt.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <sstream>
@@ -296,10 +297,20 @@ RenderSummary PathTracerApp::execute() {
     std::vector<float*> p;
     ~HostPin() { for (auto* q : p) cudaHostUnregister(q); }
   } hostPin;
+  // This thread has not touched CUDA yet (contexts are created on worker threads): select the first GPU of the device
+  // list before registering host memory, or the runtime would bring up a context on GPU 0 even when --devices leaves it out.
+  if (const cudaError_t e = cudaSetDevice(gpus[0]->device); e != cudaSuccess) throw std::runtime_error(std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+  bool pinFailureLogged = false;
+  auto pinFailed = [&](const char* what, cudaError_t e) {
+    cudaGetLastError();
+    if (!pinFailureLogged) logging::warn("Could not page-lock {} ({}): host transfers take the slower pageable path", what, cudaGetErrorString(e));
+    pinFailureLogged = true;
+  };
   if (!recordStream) {
     for (auto& f : films) {
-      if (cudaHostRegister(f.hdrData(), f.width() * f.height() * 3 * sizeof(float), cudaHostRegisterPortable) == cudaSuccess) hostPin.p.push_back(f.hdrData());
-      else cudaGetLastError();
+      const cudaError_t e = cudaHostRegister(f.hdrData(), f.width() * f.height() * 3 * sizeof(float), cudaHostRegisterPortable);
+      if (e == cudaSuccess) hostPin.p.push_back(f.hdrData());
+      else pinFailed("the host film", e);
     }
   }
   nvtxRangePop();
@@ -319,14 +330,21 @@ RenderSummary PathTracerApp::execute() {
   // read_results then run at the full link rate). Declared after `work` so that it unregisters before the lists are freed.
   struct ListPin {
     std::vector<void*> p;
+    bool holds(const void* q) const { return std::find(p.begin(), p.end(), q) != p.end(); }
     ~ListPin() { for (auto* q : p) cudaHostUnregister(q); }
   } listPin;
   if (recordStream) {
     for (RecordList* l : {&work.getWork().active(), &work.getWork().inactive()}) {
-      if (cudaHostRegister(l->data(), l->size() * sizeof(TraceRecord), cudaHostRegisterPortable) == cudaSuccess) listPin.p.push_back(l->data());
-      else cudaGetLastError();
+      const cudaError_t e = cudaHostRegister(l->data(), l->size() * sizeof(TraceRecord), cudaHostRegisterPortable);
+      if (e == cudaSuccess) listPin.p.push_back(l->data());
+      else pinFailed("the work lists", e);
     }
   }
+  // The registration is by address: swapping the two lists or copy-assigning an equal-sized list keeps the addresses, a
+  // reallocation would leave registered memory freed and the live list pageable. Checked after every re-deal.
+  auto listsStillPinned = [&]() {
+    return listPin.p.empty() || (listPin.holds(work.getWork().active().data()) && listPin.holds(work.getWork().inactive().data()));
+  };
 
   // Setup remote user interface (:618-633). Unlike the reference the state a client has not touched
   // yet starts from the command line, with or without a client.
@@ -442,7 +460,11 @@ RenderSummary PathTracerApp::execute() {
       hostProcessing.run([&, step, saveNow, exposure = state.exposure, gamma = state.gamma]() {
         Trace t("async_work");
         { Trace t1("accumulate_framebuffers"); film.accumulate(work.getWork().inactive()); }
-        if (loadBalanceEnabled && step > 1) { Trace t2("run_load_balancing"); work.allocateWorkByPathLength(); }
+        if (loadBalanceEnabled && step > 1) {
+          Trace t2("run_load_balancing");
+          work.allocateWorkByPathLength();
+          if (!listsStillPinned()) throw std::logic_error("load balancing reallocated a page-locked work list");
+        }
         { Trace t3("clear_accumulators"); totalRays = work.clearInactiveAccumulators(); }
         if (saveNow) {
           // With a UI server the full uncompressed image is transmitted at the save interval (:748-759);

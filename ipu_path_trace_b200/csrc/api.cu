@@ -112,6 +112,7 @@ int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
   }
   if ((e = cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
   if ((e = cudaEventCreateWithFlags(&c->evNextUploaded, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaEventCreateWithFlags(&c->evNextConsumed, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&c->evBegin)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&c->evEnd)) != cudaSuccess) return bail(e, "cudaEventCreate");
 
@@ -200,6 +201,7 @@ void b200pt_destroy(b200pt_ctx* c) {
   if (c->traceStream) cudaStreamSynchronize(c->traceStream);
   if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
   if (c->evNextUploaded) cudaEventDestroy(c->evNextUploaded);
+  if (c->evNextConsumed) cudaEventDestroy(c->evNextConsumed);
   c->recStagingNext.release();
   if (c->stream) cudaStreamSynchronize(c->stream);
   for (cudaEvent_t e : c->evPool) cudaEventDestroy(e);

@@ -62,11 +62,12 @@ int b200pt_set_sample_index(b200pt_ctx* c, uint32_t next) {
   return B200PT_OK;
 }
 
-// true if `p` is page-locked (cudaHostAlloc / cudaHostRegister): cudaMemcpyAsync then neither stages nor blocks
-static bool isPinned(const void* p) {
+// true only if `p` is ordinary pageable memory, which the driver has staged by the time cudaMemcpyAsync returns. Page-locked,
+// managed or partly registered ranges (and anything the query cannot classify) are read later by the copy engine.
+static bool isPageable(const void* p) {
   cudaPointerAttributes a{};
   if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
-  return a.type == cudaMemoryTypeHost;
+  return a.type == cudaMemoryTypeUnregistered;
 }
 
 int b200pt_host_alloc(void** out, size_t bytes) {
@@ -88,6 +89,9 @@ int b200pt_setup_next(b200pt_ctx* c, const b200pt_trace_record* worklist, size_t
   if (n > 0 && !worklist) return c->fail(B200PT_ERR_INVALID, "setup_next: null worklist");
   CU(c, cudaSetDevice(c->cfg.device));
   CU(c, c->recStagingNext.ensure(c->cfg.max_worklist));
+  // The unpack kernel that path_trace queued for the PREVIOUS staged list may not have run yet (the main stream can be
+  // busy with the step before it): this upload must not overwrite the buffer it reads.
+  if (c->nextConsumedRecorded) CU(c, cudaStreamWaitEvent(c->copyStream, c->evNextConsumed, 0));
   if (n > 0) CU(c, cudaMemcpyAsync(c->recStagingNext.p, worklist, n * sizeof(TraceRecord), cudaMemcpyHostToDevice, c->copyStream));
   CU(c, cudaEventRecord(c->evNextUploaded, c->copyStream));
   c->nextStaged = true;
@@ -107,9 +111,9 @@ int b200pt_setup(b200pt_ctx* c, const b200pt_trace_record* worklist, size_t n) {
   if (n == 0) return B200PT_OK;
   CU(c, cudaMemcpyAsync(c->recStaging.p, worklist, n * sizeof(TraceRecord), cudaMemcpyHostToDevice, c->stream));
   CU(c, launchUnpackRecords(c->recStaging.p, (uint32_t)n, c->pix.p, c->accum.p, c->sampleCount.p, c->pathLength.p, c->stream));
-  // A pageable host buffer has been consumed when cudaMemcpyAsync returns (the driver stages it); a page-locked one is
+  // A pageable host buffer has been consumed when cudaMemcpyAsync returns (the driver stages it); anything else is
   // read by the copy engine later, so wait for the copy - the caller owns the buffer again when setup returns.
-  if (isPinned(worklist)) CU(c, cudaStreamSynchronize(c->stream));
+  if (!isPageable(worklist)) CU(c, cudaStreamSynchronize(c->stream));
   return B200PT_OK;
 }
 
@@ -127,6 +131,8 @@ int b200pt_path_trace(b200pt_ctx* c) {
     c->nItems = c->nextItems;
     CU(c, cudaStreamWaitEvent(c->stream, c->evNextUploaded, 0));
     if (c->nItems) CU(c, launchUnpackRecords(c->recStagingNext.p, c->nItems, c->pix.p, c->accum.p, c->sampleCount.p, c->pathLength.p, c->stream));
+    CU(c, cudaEventRecord(c->evNextConsumed, c->stream));
+    c->nextConsumedRecorded = true;
   }
   c->evUsed = 0; c->spans.clear();
   c->counters = b200pt_counters{};

@@ -69,6 +69,9 @@ struct b200pt_ctx {
   DevBuf<TraceRecord> recStagingNext;
   cudaStream_t copyStream = nullptr;
   cudaEvent_t evNextUploaded = nullptr;
+  // recorded on `stream` behind the unpack kernel that reads recStagingNext: the next upload into that buffer waits for it
+  cudaEvent_t evNextConsumed = nullptr;
+  bool nextConsumedRecorded = false;
   bool nextStaged = false;
   uint32_t nextItems = 0;
   DevBuf<uint32_t> pix, sampleCount, pathLength;

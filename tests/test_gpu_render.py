@@ -173,6 +173,38 @@ def test_setup_next_and_pinned_buffers_equal_the_serial_programs(lib_built, nif_
     assert not np.array_equal(a[0]["v"], a[1]["v"])
 
 
+def test_setup_next_waits_for_the_unpack_of_the_previous_staged_list(lib_built, nif_model):
+    """setup_next(k+1) may be called while the kernel that unpacks staged list k is still QUEUED behind earlier work on the
+    context's stream; the upload must not overwrite that list (both use the one staging buffer). The stream is kept busy
+    with film clears of a 4K film so that the unpack of list B has certainly not run when list C is staged."""
+    W, H, sps = 3840, 2160, 1
+    full = lib_built.create_work_list_for_image(W, H)
+    n = 4096
+    A, B, Cc = (full[i * 100000: i * 100000 + n] for i in range(3))
+    t = lib_built.PathTracer(W, H, nif_impl=lib_built.NIF_SIMT)
+    t.init_nif_weights(nif_model); t.init_render_settings(samples_per_step=sps)
+    pins = [lib_built.PinnedRecords(n) for _ in range(3)]
+    for p, l in zip(pins, (A, B, Cc)):
+        p.array[:] = l
+    t.setup(pins[0].array)
+    t.path_trace(sync=False)
+    t.setup_next(pins[1].array)
+    got_a = t.read_results()[0].copy()
+    for _ in range(400):                      # ~100 MB memset each, asynchronous: the stream is busy for milliseconds
+        t.film_clear()
+    t.path_trace(sync=False)                  # queues unpack(B) behind the clears
+    t.setup_next(pins[2].array)               # must wait for that unpack before it overwrites the staging buffer
+    got_b = t.read_results()[0].copy()
+    t.path_trace(sync=False)
+    got_c = t.read_results()[0].copy()
+    t.close()
+    for p in pins:
+        p.close()
+    for got, want in ((got_a, A), (got_b, B), (got_c, Cc)):
+        assert np.array_equal(got["u"], want["u"]) and np.array_equal(got["v"], want["v"])
+        assert np.all(got["sampleCount"] == sps)
+
+
 def test_c5_size_properties(lib_built, nif_model):
     """BASELINE config C5's image (3840x2160 = 8.3 M work items, the largest single-GPU work list): counts, escape
     statistics, finiteness, and the film of one step equals the records (size-independent properties; the oracle needs
