@@ -192,7 +192,7 @@ trace_wavefront_kernel(const SceneSoA* __restrict__ scene, const DeviceSettings 
           const V3 d = unit(v3(cx, cy, -1.f));
           // depth 0 is below the roulette depth (b200pt_create rejects roulette_depth 0), so the first intersection
           // draws nothing: a miss is an ESCAPED record with weight 1, i.e. throughput (1,1,1) and length 1
-          if (s.rouletteDepth != 0u && closestHit(sc, o, d, n) < 0) {
+          if (closestHit(sc, o, d, n) < 0) {
             escapedUv(d, s.azimuth, uv[j].x, uv[j].y);
             escMask |= 1u << j;
           } else {
