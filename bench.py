@@ -269,6 +269,48 @@ def run_cli(n_gpus: int, width: int, height: int, spp: int, sps: int, save_inter
                 "saves": log.count("Saved images at step"), "png_and_exr_written": files_ok}
 
 
+def multi_gpu_check(pt, model, dist, rank: int, world: int, local: int):
+    """The reference's replicas render ONE image (src/PathTracerApp.cpp:205-252): a small image rendered sharded over the
+    `world` ranks and reduced over NCCL must be the image one GPU renders whole. tests/test_gpu_multi.py asserts this, but
+    needs a multi-GPU lease; this puts the same comparison where an N-GPU run actually happens. Collective: every rank calls."""
+    import torch
+    Wc, Hc, sps, steps = 208, 160, 8, 3
+
+    def render(worklist):
+        t = pt.PathTracer(Wc, Hc, device=local, max_worklist=len(worklist), nif_impl=pt.NIF_TCGEN05)
+        t.init_nif_weights(model)
+        t.init_render_settings(seed=1, samples_per_step=sps)
+        t.setup(worklist)
+        tot = [0, 0, 0]
+        for _ in range(steps):
+            t.path_trace(sync=False)
+            t.film_accumulate()
+            c = t.counters()
+            tot[0] += c.paths; tot[1] += c.escaped; tot[2] += c.path_segments
+        film = torch.zeros(Hc * Wc * 3, dtype=torch.float32, device="cuda")
+        t.film_read_device(film.data_ptr(), 1.0 / steps)
+        t.close()
+        return film, tot
+
+    shard = pt.shard_tiles(Wc, Hc, world)[rank]
+    film, tot = render(shard)
+    dist.reduce(film, dst=0)                                   # disjoint pixel support: the sum is a gather
+    counts = torch.tensor(tot + [len(shard)], dtype=torch.int64, device="cuda")
+    per_rank = [torch.zeros_like(counts) for _ in range(world)]
+    dist.all_gather(per_rank, counts)
+    torch.cuda.synchronize()
+    if rank != 0:
+        return None
+    want, want_tot = render(pt.create_work_list_for_image(Wc, Hc))
+    got_tot = [int(sum(int(x[i]) for x in per_rank)) for i in range(3)]
+    a, b = film.double(), want.double()
+    rel = ((a - b).abs() / b.abs().clamp_min(1e-7)).max().item()
+    return {"image": f"{Wc}x{Hc}, {sps * steps} spp, sharded over {world} ranks + NCCL reduce vs whole on rank 0",
+            "max_rel_diff": rel, "bit_equal": bool(torch.equal(film, want)),
+            "counters_equal": got_tot == [int(x) for x in want_tot], "paths": got_tot[0], "escaped": got_tot[1], "path_segments": got_tot[2],
+            "items_per_rank": [int(x[3]) for x in per_rank]}
+
+
 # ---------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------
@@ -399,6 +441,13 @@ def run_ours(args) -> None:
             extras["c4"] = run_c4(tracer, flops_per_eval)
         except Exception as e:      # an extra must never lose the headline
             extras["c4"] = {"error": repr(e)[:300]}
+    if dist is not None and not args.no_extras:
+        try:
+            chk = multi_gpu_check(pt, model, dist, rank, world, local)
+        except Exception as e:
+            chk = {"error": repr(e)[:300]}
+        if rank == 0:
+            extras["multi_gpu_check"] = chk
     tracer.close()
     tracer = None
     pin_in.close(); pin_out.close()

@@ -265,8 +265,22 @@ void writeExr(const std::string& path, const float* bgr, uint32_t width, uint32_
         for (uint32_t x = 0; x < width; ++x) *dst++ = src[(size_t)x * 3];
       }
     const std::vector<uint8_t> pre = zipPrecondition(raw.data(), raw.size());
-    std::vector<uint8_t> z = deflateAll(pre.data(), pre.size(), 4);
-    packed[b] = z.size() < raw.size() ? std::move(z) : std::move(raw);
+    // fp32 Monte-Carlo noise barely compresses (a 4K render: 0.6 %), and deflating it then costs more than the rest of
+    // the save. Probe four 16 KiB pieces spread over the pre-conditioned block at level 1; a block that would shrink by
+    // less than 5 % is stored raw, which is the format's own rule for blocks that do not shrink.
+    bool worthDeflating = true;
+    constexpr size_t kPiece = 16u << 10;
+    if (pre.size() >= 16 * kPiece) {
+      std::vector<uint8_t> probe(4 * kPiece);
+      for (size_t k = 0; k < 4; ++k) std::memcpy(probe.data() + k * kPiece, pre.data() + k * (pre.size() / 4), kPiece);
+      worthDeflating = deflateAll(probe.data(), probe.size(), 1).size() < probe.size() - probe.size() / 20;
+    }
+    if (worthDeflating) {
+      std::vector<uint8_t> z = deflateAll(pre.data(), pre.size(), 4);
+      packed[b] = z.size() < raw.size() ? std::move(z) : std::move(raw);
+    } else {
+      packed[b] = std::move(raw);
+    }
   }
   for (uint32_t b = 0; b < blocks; ++b) {
     const uint64_t off = out.size();

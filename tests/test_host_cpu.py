@@ -169,11 +169,15 @@ def test_png_exr_round_trip_and_interop(host, tmp_path, w, h):
     img8 = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
     imgf = (rng.standard_normal((h, w, 3)) * 10).astype(np.float32)
     imgf[0, 0] = [0.0, 1e-30, 6.5e4]
+    if h >= 1000:      # upper half smooth (deflated blocks), lower half noise (blocks the writer's probe stores raw): both in one file
+        imgf[: h // 2] = (np.arange(w, dtype=np.float32)[None, :, None] / w + np.arange(h // 2, dtype=np.float32)[:, None, None] / h)
     p, e = str(tmp_path / "a.png").encode(), str(tmp_path / "a.exr").encode()
     assert host.b200host_write_png(p, img8.ctypes.data_as(C.c_void_p), w, h) == 0
     assert host.b200host_write_exr(e, imgf.ctypes.data_as(C.c_void_p), w, h) == 0
     assert np.array_equal(cv2.imread(p.decode(), cv2.IMREAD_UNCHANGED).reshape(h, w, 3), img8)
     assert np.array_equal(cv2.imread(e.decode(), cv2.IMREAD_UNCHANGED).reshape(h, w, 3), imgf)
+    if h >= 1000:
+        assert 0.55 * imgf.nbytes < os.path.getsize(e) < 0.95 * imgf.nbytes       # the smooth half shrank, the noise half was stored
     # our readers on our files
     ww, hh = C.c_uint32(), C.c_uint32()
     back8 = np.zeros_like(img8)
