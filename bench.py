@@ -51,15 +51,29 @@ def measured_peaks():
     return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
 
 
+NIF_KERNEL_SOURCES = ("nif_tc.cu", "nif_common.cuh", "api_nif.cu")
+
+
+def nif_source_hashes():
+    import hashlib
+    d = os.path.join(ROOT, "ipu_path_trace_b200", "csrc")
+    return {f: hashlib.sha256(open(os.path.join(d, f), "rb").read()).hexdigest() for f in NIF_KERNEL_SOURCES}
+
+
 def nif_traffic_bytes():
-    """dram__bytes_read.sum + dram__bytes_write.sum of ONE nif_tc_kernel launch of this very workload
-    (one wavefront of C2), from the committed `ncu --set full` capture (profiles/r2_nif_tc_traffic.json);
-    None when no capture has been committed."""
-    p = os.path.join(ROOT, "profiles", "r2_nif_tc_traffic.json")
-    if not os.path.exists(p):
-        return None
-    d = json.load(open(p))
-    return float(d["dram_bytes_read_per_launch"]) + float(d["dram_bytes_write_per_launch"])
+    """(bytes, note): dram__bytes_read.sum + dram__bytes_write.sum of ONE nif_tc_kernel launch of this very workload (one
+    wavefront of C2) from the newest committed `ncu --set full` capture, profiles/r*_nif_tc_traffic.json - ncu cannot run
+    inside the timed region. A capture is only used if it records the hashes of the kernel's sources and they are those of
+    the files in this tree (scratch/make_traffic_json.py writes them); otherwise (None, why), never a stale constant."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_nif_tc_traffic.json")), reverse=True)
+    if not files:
+        return None, "no capture committed"
+    d = json.load(open(files[0]))
+    name = os.path.basename(files[0])
+    if d.get("source_sha256") != nif_source_hashes():
+        return None, f"profiles/{name} was captured from other kernel sources than this tree's (source_sha256 differs or is absent): re-capture"
+    return float(d["dram_bytes_read_per_launch"]) + float(d["dram_bytes_write_per_launch"]), f"profiles/{name}"
 
 
 class ClockSampler:
@@ -490,7 +504,7 @@ def run_ours(args) -> None:
             "gpu_launches": int(launches),
             "clocks": clk,
             "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
-                         "traffic": nif_traffic_bytes(), "kernel": "nif_tc_kernel", "peak_source": peak_src,
+                         "traffic": nif_traffic_bytes()[0], "traffic_source": nif_traffic_bytes()[1], "kernel": "nif_tc_kernel", "peak_source": peak_src,
                          "whole_step_frac": (flops_per_eval * escaped / world) / (dev_ms * 1e-3) / 1e12 / peak_tf if dev_ms > 0 else 0.0},
         }
         line["config"].update(extras)

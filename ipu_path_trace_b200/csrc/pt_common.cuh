@@ -159,22 +159,34 @@ __device__ __forceinline__ void reproSinCosTurn(float t, float& s, float& c) {  
 }
 
 // normal: N(0,1) (poprand::normal, PathTracerApp.cpp:34-37); uniform: U(-1,1) (:30-33);
-// truncated-normal: N(0,1) clamped to +-3 sigma (:38-41).
-__device__ __forceinline__ void aaNoisePair(uint32_t w0, uint32_t w1, int type, float& n0, float& n1) {
+// truncated-normal: N(0,1) conditioned on |x| <= 3 sigma (:38-41, poprand::truncatedNormal with alpha 3) by re-drawing: a pair
+// with a component beyond 3 sigma (0.54 % of the pairs) is rejected and replaced by the next candidate pair, taken from
+// Philox blocks keyed by the rejected words themselves (counter = (w0, w1, attempt, "trun")), so the path's own stream, and
+// with it every later draw of the path, stays where it is.
+__device__ __forceinline__ void boxMullerPair(uint32_t w0, uint32_t w1, float& a, float& b) {
   const float u1 = (float)((w0 >> 8) + 1u) * 5.9604644775390625e-8f;   // (0,1]
   const float u2 = (float)(w1 >> 8) * 5.9604644775390625e-8f;          // [0,1)
+  const float r = sqrtf(-2.f * reproLog(u1));
+  float s, c;
+  reproSinCosTurn(u2, s, c);
+  a = r * c; b = r * s;
+}
+__device__ __forceinline__ void aaNoisePair(uint32_t w0, uint32_t w1, int type, float& n0, float& n1) {
   if (type == 1) {
+    const float u1 = (float)((w0 >> 8) + 1u) * 5.9604644775390625e-8f;   // (0,1]
+    const float u2 = (float)(w1 >> 8) * 5.9604644775390625e-8f;          // [0,1)
     n0 = roundToHalf(2.f * u1 - 1.f);
     n1 = roundToHalf(2.f * u2 - 1.f);
     return;
   }
-  const float r = sqrtf(-2.f * reproLog(u1));
-  float s, c;
-  reproSinCosTurn(u2, s, c);
-  float a = r * c, b = r * s;
+  float a, b;
+  boxMullerPair(w0, w1, a, b);
   if (type == 2) {
-    a = a > 3.f ? 3.f : (a < -3.f ? -3.f : a);
-    b = b > 3.f ? 3.f : (b < -3.f ? -3.f : b);
+    for (uint32_t attempt = 0; fabsf(a) > 3.f || fabsf(b) > 3.f; ++attempt) {
+      const Philox4 p = philox4x32_10(w0, w1, attempt, 0x7472756eu, 0u, 0u);
+      boxMullerPair(p.v[0], p.v[1], a, b);
+      if (fabsf(a) > 3.f || fabsf(b) > 3.f) boxMullerPair(p.v[2], p.v[3], a, b);
+    }
   }
   n0 = roundToHalf(a);
   n1 = roundToHalf(b);

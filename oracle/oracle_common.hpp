@@ -168,23 +168,34 @@ enum AaNoiseType { AA_NORMAL = 0, AA_UNIFORM = 1, AA_TRUNCATED_NORMAL = 2 };
 
 // Two anti-alias noise values (as binary16-rounded floats) from two Philox words.
 // normal: N(0,1) (poprand::normal, PathTracerApp.cpp:34-37); uniform: U(-1,1) (:30-33);
-// truncated-normal: N(0,1) limited to +-3 sigma (:38-41) - drawn by clamping here, the
-// IPU library redraws; the tails beyond 3 sigma hold 0.27 % of the mass.
-inline void aaNoisePair(std::uint32_t w0, std::uint32_t w1, int type, float& n0, float& n1) {
+// truncated-normal: N(0,1) conditioned on |x| <= 3 sigma (:38-41, poprand::truncatedNormal, alpha 3), by re-drawing like the
+// IPU library: a pair with a component beyond 3 sigma is replaced by the next candidate pair from Philox blocks whose
+// counter is (w0, w1, attempt, "trun"), key 0 - the path's own stream does not advance. The IPU generator itself is not
+// reproducible, so the words are this repository's choice; product and oracle share it.
+inline void boxMullerPair(std::uint32_t w0, std::uint32_t w1, float& a, float& b) {
   const float u1 = (float)((w0 >> 8) + 1u) * 5.9604644775390625e-8f;   // (0,1]
   const float u2 = (float)(w1 >> 8) * 5.9604644775390625e-8f;          // [0,1)
+  const float r = std::sqrt(-2.f * reproLog(u1));
+  float s, c;
+  reproSinCosTurn(u2, s, c);
+  a = r * c; b = r * s;
+}
+inline void aaNoisePair(std::uint32_t w0, std::uint32_t w1, int type, float& n0, float& n1) {
   if (type == AA_UNIFORM) {
+    const float u1 = (float)((w0 >> 8) + 1u) * 5.9604644775390625e-8f;   // (0,1]
+    const float u2 = (float)(w1 >> 8) * 5.9604644775390625e-8f;          // [0,1)
     n0 = roundToHalf(2.f * u1 - 1.f);
     n1 = roundToHalf(2.f * u2 - 1.f);
     return;
   }
-  const float r = std::sqrt(-2.f * reproLog(u1));
-  float s, c;
-  reproSinCosTurn(u2, s, c);
-  float a = r * c, b = r * s;
+  float a, b;
+  boxMullerPair(w0, w1, a, b);
   if (type == AA_TRUNCATED_NORMAL) {
-    a = a > 3.f ? 3.f : (a < -3.f ? -3.f : a);
-    b = b > 3.f ? 3.f : (b < -3.f ? -3.f : b);
+    for (std::uint32_t attempt = 0; std::fabs(a) > 3.f || std::fabs(b) > 3.f; ++attempt) {
+      const Philox4 p = philox4x32_10(w0, w1, attempt, 0x7472756eu, 0u, 0u);
+      boxMullerPair(p.v[0], p.v[1], a, b);
+      if (std::fabs(a) > 3.f || std::fabs(b) > 3.f) boxMullerPair(p.v[2], p.v[3], a, b);
+    }
   }
   n0 = roundToHalf(a);
   n1 = roundToHalf(b);

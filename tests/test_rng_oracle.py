@@ -21,8 +21,19 @@ def test_aa_noise_moments(orc):
     assert abs(n.mean()) < 0.01 and abs(n.std() - 1.0) < 0.01        # poprand::normal(0,1), PathTracerApp.cpp:34-37
     u = orc.half_to_float(orc.aa_noise(w, 1))
     assert u.min() >= -1 and u.max() <= 1 and abs(u.std() - 1 / np.sqrt(3)) < 0.01   # uniform(-1,1) :30-33
-    t = orc.half_to_float(orc.aa_noise(w, 2))
-    assert np.abs(t).max() <= 3.0                                      # truncated normal :38-41
+    # truncated normal :38-41 is a conditional distribution (re-draw), not a clamp: nothing piles up at the bounds
+    # (a clamp leaves 0.27 % of the samples at exactly +-3; binary16 rounding of values just below 3 leaves ~1e-5),
+    # the variance is that of N(0,1) given |x| <= 3, and pairs that needed no re-draw are the plain normal's
+    w = rng.integers(0, 2**32, 2000000, dtype=np.uint64).astype(np.uint32)
+    n = orc.half_to_float(orc.aa_noise(w, 0)).reshape(-1, 2)
+    t = orc.half_to_float(orc.aa_noise(w, 2)).reshape(-1, 2)
+    assert np.abs(t).max() <= 3.0
+    assert np.mean(np.abs(t) == 3.0) < 1e-4
+    assert abs(t.var() - 0.97334) < 0.004 and abs(t.mean()) < 0.003
+    kept = np.abs(n).max(axis=1) < 3.0            # strict: binary16 rounding maps values a hair beyond 3 onto 3.0
+    assert np.array_equal(t[kept], n[kept]) and 0.003 < 1 - kept.mean() < 0.008
+    redrawn = t[~kept]
+    assert abs(redrawn.var() - 0.97334) < 0.1 and abs(redrawn.mean()) < 0.05      # the replacement pairs are themselves truncated normals
 
 
 def test_half_conversion_matches_numpy(orc):
