@@ -426,19 +426,34 @@ RenderSummary PathTracerApp::execute() {
     // Run path tracing on the GPUs (setup / path_trace / read_results, :690-694). Results go into the
     // active buffer whilst the async host task processes the last result from the inactive buffer.
     nvtxRangePushA("ipu_render");
-    if (recordStream) {
-      if (loadBalanceEnabled) logging::debug("Work list order digest at step {}: {}", step, work.activeOrderDigest());
-      for (std::size_t g = 0; g < gpus.size(); ++g) check(b200pt_setup(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), *gpus[g], "setup");
+    if (recordStream && loadBalanceEnabled) logging::debug("Work list order digest at step {}: {}", step, work.activeOrderDigest());
+    // One host thread per GPU for the step's programs: enqueueing a path_trace costs a few hundred microseconds of driver
+    // calls, and reading a GPU's counters waits for that GPU - done from one thread, GPU 7 would start its step only after
+    // the seven enqueues before it and every step would begin with idle devices. A context is still only ever used by one
+    // thread at a time (the threads are joined before anything else touches it).
+    std::vector<b200pt_counters> ctrs(gpus.size());
+    auto renderOn = [&](std::size_t g) {
+      Gpu& gpu = *gpus[g];
+      if (recordStream) check(b200pt_setup(gpu.ctx, work.jobSlice(work.getWork().active(), g), work.jobSize()), gpu, "setup");
+      check(b200pt_path_trace(gpu.ctx), gpu, "path_trace");                      // asynchronous
+      if (recordStream) check(b200pt_read_results(gpu.ctx, work.jobSlice(work.getWork().active(), g), work.jobSize(), &ctrs[g]), gpu, "read_results");
+      else {
+        check(b200pt_film_accumulate(gpu.ctx), gpu, "film_accumulate");
+        check(b200pt_get_counters(gpu.ctx, &ctrs[g]), gpu, "sync");
+      }
+    };
+    if (gpus.size() == 1) renderOn(0);
+    else {
+      std::vector<std::exception_ptr> errors(gpus.size());
+      std::vector<std::thread> workers;
+      for (std::size_t g = 0; g < gpus.size(); ++g)
+        workers.emplace_back([&, g] { try { renderOn(g); } catch (...) { errors[g] = std::current_exception(); } });
+      for (auto& w : workers) w.join();
+      for (auto& e : errors) if (e) std::rethrow_exception(e);
     }
-    for (auto& g : gpus) check(b200pt_path_trace(g->ctx), *g, "path_trace");     // asynchronous: all GPUs run concurrently
     std::size_t stepRays = 0;
     for (std::size_t g = 0; g < gpus.size(); ++g) {
-      b200pt_counters ctr{};
-      if (recordStream) check(b200pt_read_results(gpus[g]->ctx, work.jobSlice(work.getWork().active(), g), work.jobSize(), &ctr), *gpus[g], "read_results");
-      else {
-        check(b200pt_film_accumulate(gpus[g]->ctx), *gpus[g], "film_accumulate");
-        check(b200pt_get_counters(gpus[g]->ctx, &ctr), *gpus[g], "sync");
-      }
+      const b200pt_counters& ctr = ctrs[g];
       summary.paths += ctr.paths; summary.escaped += ctr.escaped; summary.rays += ctr.path_segments;
       summary.traceMs += ctr.trace_ms; summary.nifMs += ctr.nif_ms; summary.deviceMs = std::max(summary.deviceMs, 0.0) + ctr.total_ms / gpus.size();
       stepRays += ctr.path_segments;
