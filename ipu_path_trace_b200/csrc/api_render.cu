@@ -164,7 +164,7 @@ int b200pt_path_trace(b200pt_ctx* c) {
     CU(c, cudaMemsetAsync(qCount, 0, sizeof(uint32_t), ts));
     CU(c, cudaEventRecord(e0, ts));
     CU(c, launchTraceWavefront(c->scene.p, c->settings, c->pix.p, c->nItems, c->nextSample + done, k, qUv, qThr,
-                               qCount, c->sampleCount.p, c->pathLength.p, c->stats.p, reinterpret_cast<float*>(c->accum.p), c->liveScratch.p, c->escScratch.p, c->traceVariant, ts));
+                               qCount, c->sampleCount.p, c->pathLength.p, c->stats.p, c->accum.p, c->liveScratch.p, c->escScratch.p, c->traceVariant, ts));
     CU(c, cudaEventRecord(e1, ts));
     if (ov) {
       CU(c, cudaEventRecord(c->evTraced[q], ts));
@@ -173,7 +173,7 @@ int b200pt_path_trace(b200pt_ctx* c) {
     NifIo io{};
     io.uv = qUv; io.thrSlot = qThr; io.count = qCount;
     io.countHost = (uint32_t)std::min<size_t>((size_t)c->nItems * k, 0xffffffffu);
-    io.bgrOut = nullptr; io.accum = reinterpret_cast<float*>(c->accum.p);
+    io.bgrOut = nullptr; io.accum = c->accum.p;
     CU(c, cudaEventRecord(e2, c->stream));
     rc = launchNif(c, io, B200PT_NIF_AUTO, &used);
     if (rc) return rc;

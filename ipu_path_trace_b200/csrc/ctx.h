@@ -75,7 +75,7 @@ struct b200pt_ctx {
   bool nextStaged = false;
   uint32_t nextItems = 0;
   DevBuf<uint32_t> pix, sampleCount, pathLength;
-  DevBuf<float4> accum;
+  DevBuf<AccumSlot> accum;
   // wavefront queue
   DevBuf<float2> qUv, qUvB;             // two queues: one being filled while the other is shaded
   DevBuf<float4> qThrSlot, qThrSlotB;

@@ -6,27 +6,27 @@ namespace b2 {
 
 // "setup": TraceRecord[] (20-byte AoS as the reference streams it, PathTracerApp.cpp:426) -> SoA.
 __global__ void unpack_records_kernel(const TraceRecord* __restrict__ rec, uint32_t n, uint32_t* __restrict__ pix,
-                                      float4* __restrict__ accum, uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength) {
+                                      AccumSlot* __restrict__ accum, uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const TraceRecord r = rec[i];
   pix[i] = (uint32_t)r.u | ((uint32_t)r.v << 16);
-  accum[i] = make_float4(r.r, r.g, r.b, 0.f);
+  accum[i] = AccumSlot{accumToFixed(r.r), accumToFixed(r.g), accumToFixed(r.b), 0};
   sampleCount[i] = r.sampleCount;
   pathLength[i] = r.pathLength;
 }
 
 // "read_results": SoA -> TraceRecord[]; the two counters wrap like the reference's uint16 fields.
 __global__ void pack_records_kernel(TraceRecord* __restrict__ rec, uint32_t n, const uint32_t* __restrict__ pix,
-                                    const float4* __restrict__ accum, const uint32_t* __restrict__ sampleCount,
+                                    const AccumSlot* __restrict__ accum, const uint32_t* __restrict__ sampleCount,
                                     const uint32_t* __restrict__ pathLength) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   TraceRecord r;
   const uint32_t p = pix[i];
-  const float4 a = accum[i];
+  const AccumSlot a = accum[i];
   r.u = (uint16_t)(p & 0xffffu); r.v = (uint16_t)(p >> 16);
-  r.r = a.x; r.g = a.y; r.b = a.z;
+  r.r = accumToFloat(a.r); r.g = accumToFloat(a.g); r.b = accumToFloat(a.b);
   r.sampleCount = (uint16_t)sampleCount[i];
   r.pathLength = (uint16_t)pathLength[i];
   rec[i] = r;
@@ -35,7 +35,7 @@ __global__ void pack_records_kernel(TraceRecord* __restrict__ rec, uint32_t n, c
 // AccumulatedImage::accumulate (AccumulatedImage.cpp:59-74): hdr(v,u) += (b,g,r)/sampleCount for
 // valid items, then LoadBalancer::clearInactiveAccumulators. One work item owns one pixel, so
 // no atomics are needed.
-__global__ void film_accumulate_kernel(uint32_t n, const uint32_t* __restrict__ pix, float4* __restrict__ accum,
+__global__ void film_accumulate_kernel(uint32_t n, const uint32_t* __restrict__ pix, AccumSlot* __restrict__ accum,
                                        uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength,
                                        float* __restrict__ film, uint32_t width, uint32_t height) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -44,12 +44,12 @@ __global__ void film_accumulate_kernel(uint32_t n, const uint32_t* __restrict__ 
   const uint32_t u = p & 0xffffu, v = p >> 16;
   const uint32_t sc = sampleCount[i];
   if (u < width && v < height && sc > 0) {
-    const float4 a = accum[i];
+    const AccumSlot a = accum[i];
     const float inv = 1.f / (float)sc;
     float* px = film + 3 * ((size_t)v * width + u);
-    px[0] += a.z * inv; px[1] += a.y * inv; px[2] += a.x * inv;      // stored B,G,R (:70)
+    px[0] += accumToFloat(a.b) * inv; px[1] += accumToFloat(a.g) * inv; px[2] += accumToFloat(a.r) * inv;      // stored B,G,R (:70)
   }
-  accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  accum[i] = AccumSlot{0, 0, 0, 0};
   sampleCount[i] = 0;
   pathLength[i] = 0;
 }
@@ -72,19 +72,19 @@ __global__ void film_tonemap_kernel(const float* __restrict__ film, uint8_t* __r
 
 static inline uint32_t blocksFor(size_t n, int t) { return (uint32_t)((n + t - 1) / t); }
 
-cudaError_t launchUnpackRecords(const TraceRecord* rec, uint32_t n, uint32_t* pix, float4* accum, uint32_t* sampleCount,
+cudaError_t launchUnpackRecords(const TraceRecord* rec, uint32_t n, uint32_t* pix, AccumSlot* accum, uint32_t* sampleCount,
                                 uint32_t* pathLength, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   unpack_records_kernel<<<blocksFor(n, 256), 256, 0, stream>>>(rec, n, pix, accum, sampleCount, pathLength);
   return cudaGetLastError();
 }
-cudaError_t launchPackRecords(TraceRecord* rec, uint32_t n, const uint32_t* pix, const float4* accum, const uint32_t* sampleCount,
+cudaError_t launchPackRecords(TraceRecord* rec, uint32_t n, const uint32_t* pix, const AccumSlot* accum, const uint32_t* sampleCount,
                               const uint32_t* pathLength, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   pack_records_kernel<<<blocksFor(n, 256), 256, 0, stream>>>(rec, n, pix, accum, sampleCount, pathLength);
   return cudaGetLastError();
 }
-cudaError_t launchFilmAccumulate(uint32_t n, const uint32_t* pix, float4* accum, uint32_t* sampleCount, uint32_t* pathLength,
+cudaError_t launchFilmAccumulate(uint32_t n, const uint32_t* pix, AccumSlot* accum, uint32_t* sampleCount, uint32_t* pathLength,
                                  float* filmBgr, uint32_t width, uint32_t height, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   film_accumulate_kernel<<<blocksFor(n, 256), 256, 0, stream>>>(n, pix, accum, sampleCount, pathLength, filmBgr, width, height);

@@ -13,7 +13,7 @@ namespace b2 {
 // ---- path tracing (trace_kernels.cu) -----------------------------------------------------
 cudaError_t launchTraceWavefront(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                                  float2* qUv, float4* qThrSlot, uint32_t* qCount, uint32_t* sampleCount,
-                                 uint32_t* pathLength, unsigned long long* stats, float* accum, uint4* liveScratch, float4* escScratch, int variant,
+                                 uint32_t* pathLength, unsigned long long* stats, AccumSlot* accum, uint4* liveScratch, float4* escScratch, int variant,
                                  cudaStream_t stream);
 // entries of the live-ray list (uint4 each) and of the escape list (2 x float4 each) for up to maxItems work items
 size_t traceScratchEntries(uint32_t maxItems);
@@ -34,7 +34,7 @@ struct NifIo {
   const uint32_t* count;     // device-resident row count (the wavefront queue length) or null
   uint32_t countHost;        // used when count == null
   float* bgrOut;             // n x 3 network outputs B,G,R (inference entry points) or null
-  float* accum;              // work-item accumulators, 4 floats per slot (r,g,b,unused) or null
+  AccumSlot* accum;          // work-item accumulators (fixed point, pt_common.cuh) or null
 };
 
 // Generic description used by the SIMT kernel: fp32 copies of the binary16 parameters.
@@ -97,11 +97,11 @@ cudaError_t launchNifFeatures(uint32_t n, const float* uvIn, int inStride, float
 cudaError_t launchPackUv(uint32_t n, const float* u, const float* v, float2* uv, cudaStream_t stream);
 
 // ---- film / records (film_kernels.cu) ------------------------------------------------------
-cudaError_t launchUnpackRecords(const TraceRecord* rec, uint32_t n, uint32_t* pix, float4* accum, uint32_t* sampleCount,
+cudaError_t launchUnpackRecords(const TraceRecord* rec, uint32_t n, uint32_t* pix, AccumSlot* accum, uint32_t* sampleCount,
                                 uint32_t* pathLength, cudaStream_t stream);
-cudaError_t launchPackRecords(TraceRecord* rec, uint32_t n, const uint32_t* pix, const float4* accum, const uint32_t* sampleCount,
+cudaError_t launchPackRecords(TraceRecord* rec, uint32_t n, const uint32_t* pix, const AccumSlot* accum, const uint32_t* sampleCount,
                               const uint32_t* pathLength, cudaStream_t stream);
-cudaError_t launchFilmAccumulate(uint32_t n, const uint32_t* pix, float4* accum, uint32_t* sampleCount, uint32_t* pathLength,
+cudaError_t launchFilmAccumulate(uint32_t n, const uint32_t* pix, AccumSlot* accum, uint32_t* sampleCount, uint32_t* pathLength,
                                  float* filmBgr, uint32_t width, uint32_t height, cudaStream_t stream);
 cudaError_t launchFilmScale(const float* filmBgr, float* out, size_t n, float scale, cudaStream_t stream);
 cudaError_t launchFilmTonemap(const float* filmBgr, uint8_t* out, size_t n, float scale, float exposure, float gamma, cudaStream_t stream);

@@ -55,11 +55,7 @@ __device__ __forceinline__ void nifEmit(const NifIo& io, uint32_t row, float b, 
     io.bgrOut[3 * (size_t)row + 2] = r;
   }
   if (io.accum) {
-    const uint32_t slot = __float_as_uint(thrSlot.w);
-    float* a = io.accum + 4 * (size_t)slot;
-    atomicAdd(a, r * thrSlot.x);
-    atomicAdd(a + 1, g * thrSlot.y);
-    atomicAdd(a + 2, b * thrSlot.z);
+    accumAdd(io.accum, __float_as_uint(thrSlot.w), r * thrSlot.x, g * thrSlot.y, b * thrSlot.z);
   }
 }
 

@@ -27,6 +27,25 @@ struct TraceRecord {            // src/codelets/TraceRecord.hpp:7-19
 #pragma pack(pop)
 static_assert(sizeof(TraceRecord) == 20, "TraceRecord must stay 20 bytes");
 
+// Work-item radiance accumulator. The reference folds a pixel's samples in a fixed order (codelets.cpp:235-306), so its
+// image is a function of the seed. Here samples of one pixel finish on different SMs in no particular order; added as
+// fp32 the sum would depend on that order (run to run, and on how many GPUs share the image). Integer addition commutes:
+// every contribution is converted once to signed 64-bit fixed point with 32 fraction bits (2^-32 = 2.3e-10 absolute
+// resolution; 2^31 = 2.1e9 of headroom for the sum of a step) and added with a 64-bit integer atomic, and the sum is
+// converted back to fp32 once, when the records are packed or the film is accumulated. Same bits on every run and every
+// sharding.
+struct __align__(32) AccumSlot { long long r, g, b, unused; };
+constexpr float kAccumScale = 4294967296.f;            // 2^32
+constexpr float kAccumInvScale = 2.3283064365386963e-10f;
+__device__ __forceinline__ long long accumToFixed(float x) { return __float2ll_rn(x * kAccumScale); }
+__device__ __forceinline__ float accumToFloat(long long v) { return __ll2float_rn(v) * kAccumInvScale; }     // one rounding: the scale is a power of two
+__device__ __forceinline__ void accumAdd(AccumSlot* __restrict__ accum, uint32_t slot, float r, float g, float b) {
+  unsigned long long* a = reinterpret_cast<unsigned long long*>(accum + slot);
+  atomicAdd(a, (unsigned long long)accumToFixed(r));
+  atomicAdd(a + 1, (unsigned long long)accumToFixed(g));
+  atomicAdd(a + 2, (unsigned long long)accumToFixed(b));
+}
+
 // Render settings as the kernels see them. Quantities the reference streams as `half`
 // (PathTracerApp.cpp:339-346, IpuPathTraceJob.cpp:133-138) are stored already rounded.
 struct DeviceSettings {

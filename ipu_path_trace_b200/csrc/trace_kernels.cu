@@ -22,11 +22,9 @@ __device__ __forceinline__ void stageScene(SceneSoA& dst, const SceneSoA* __rest
 constexpr int kTraceThreads = 256;
 
 // A path that ended on an emitter (EMIT record, codelets.cpp:192-196) needs no NIF lookup: its radiance goes straight into the
-// work item's accumulator, with the same fp32 atomics the NIF kernel uses for escaped paths (nif_common.cuh nifEmit).
-__device__ __forceinline__ void emitRadiance(float* __restrict__ accum, uint32_t slot, V3 radiance) {
-  atomicAdd(accum + 4 * (size_t)slot, radiance.x);
-  atomicAdd(accum + 4 * (size_t)slot + 1, radiance.y);
-  atomicAdd(accum + 4 * (size_t)slot + 2, radiance.z);
+// work item's accumulator, with the same fixed-point atomics the NIF kernel uses for escaped paths (nif_common.cuh nifEmit).
+__device__ __forceinline__ void emitRadiance(AccumSlot* __restrict__ accum, uint32_t slot, V3 radiance) {
+  accumAdd(accum, slot, radiance.x, radiance.y, radiance.z);
 }
 
 // v1 (default): one thread carries a whole path per sample; lanes whose path has ended idle until the longest path of the
@@ -35,7 +33,7 @@ __global__ void __launch_bounds__(kTraceThreads)
 trace_wavefront_kernel_v1(const SceneSoA* __restrict__ scene, const DeviceSettings s, const uint32_t* __restrict__ pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                        float2* __restrict__ qUv, float4* __restrict__ qThrSlot, uint32_t* __restrict__ qCount,
                        uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength,
-                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */, float* __restrict__ accum) {
+                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */, AccumSlot* __restrict__ accum) {
   __shared__ SceneSoA sc;
   __shared__ uint32_t warpCount[kTraceThreads / 32];
   __shared__ uint32_t blockBase;
@@ -142,7 +140,7 @@ __global__ void __launch_bounds__(kTraceThreads)
 trace_wavefront_kernel(const SceneSoA* __restrict__ scene, const DeviceSettings s, const uint32_t* __restrict__ pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                        float2* __restrict__ qUv, float4* __restrict__ qThrSlot, uint32_t* __restrict__ qCount,
                        uint32_t* __restrict__ sampleCount, uint32_t* __restrict__ pathLength,
-                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */, float* __restrict__ accum,
+                       unsigned long long* __restrict__ stats /* [0] paths [1] escaped [2] segments */, AccumSlot* __restrict__ accum,
                        uint4* __restrict__ liveScratch, float4* __restrict__ escScratch, uint32_t phase2Warps) {
   __shared__ SceneSoA sc;
   __shared__ uint32_t warpCount[kTraceThreads / 32];
@@ -339,7 +337,7 @@ size_t traceScratchEntries(uint32_t maxItems) {
 
 cudaError_t launchTraceWavefront(const SceneSoA* scene, const DeviceSettings& s, const uint32_t* pix, uint32_t nItems, uint32_t sampleBegin, uint32_t samplesPerLaunch,
                                  float2* qUv, float4* qThrSlot, uint32_t* qCount, uint32_t* sampleCount,
-                                 uint32_t* pathLength, unsigned long long* stats, float* accum, uint4* liveScratch, float4* escScratch, int variant,
+                                 uint32_t* pathLength, unsigned long long* stats, AccumSlot* accum, uint4* liveScratch, float4* escScratch, int variant,
                                  cudaStream_t stream) {
   if (nItems == 0) return cudaSuccess;
   if (variant == 1 || !liveScratch || !escScratch) {

@@ -58,7 +58,7 @@ def test_torchrun_ranks_render_the_single_gpu_image(lib_built, nif_model, tmp_pa
     assert all(x["items"] > 0 for x in ranks)
     got = np.load(tmp_path / "film.npy")
     assert got.shape == (H, W, 3)
-    np.testing.assert_allclose(got, want, rtol=2e-6, atol=1e-7)       # fp32 atomics: addition order only
+    assert np.array_equal(got, want)      # fixed-point integer accumulation: the same bits however the image is sharded
 
 
 def test_cli_two_gpus_equal_one(lib_built, nif_model, tmp_path):

@@ -205,6 +205,27 @@ def test_setup_next_waits_for_the_unpack_of_the_previous_staged_list(lib_built, 
         assert np.all(got["sampleCount"] == sps)
 
 
+def test_two_runs_give_the_same_bits(lib_built, nif_model):
+    """The reference folds a pixel's samples in a fixed order (codelets.cpp:235-306): its image is a function of the seed.
+    Here samples finish in no particular order, so radiance is accumulated as 64-bit fixed point with integer atomics
+    (pt_common.cuh AccumSlot): two renders - also with different wavefront sizes and with the two stream schedules - must
+    give bit-identical records and films."""
+    W, H, sps = 160, 96, 24
+    outs = []
+    for kw in (dict(), dict(), dict(samples_per_launch=5), dict(samples_per_launch=24)):
+        t = lib_built.PathTracer(W, H, **kw)
+        t.init_nif_weights(nif_model); t.init_render_settings(seed=3, samples_per_step=sps)
+        t.setup(lib_built.create_work_list_for_image(W, H))
+        t.path_trace()
+        rec = t.read_results()[0].copy()
+        t.film_accumulate()
+        outs.append((rec, t.film_read()))
+        t.close()
+    for rec, film in outs[1:]:
+        assert np.array_equal(rec, outs[0][0]) and np.array_equal(film, outs[0][1])
+    assert np.isfinite(outs[0][1]).all() and outs[0][1].max() > 0
+
+
 def test_c5_size_properties(lib_built, nif_model):
     """BASELINE config C5's image (3840x2160 = 8.3 M work items, the largest single-GPU work list): counts, escape
     statistics, finiteness, and the film of one step equals the records (size-independent properties; the oracle needs
