@@ -155,6 +155,11 @@ int b200pt_host_free(void* p);
 int b200pt_path_trace(b200pt_ctx* ctx);
 int b200pt_sync(b200pt_ctx* ctx);
 
+/* Accumulation is order-independent: between setup and read_results / film_accumulate a work item's r,g,b live on the device as
+ * signed 64-bit fixed point with 32 fraction bits and are added with integer atomics, so the same seed gives the same bits on
+ * every run and for every split of the image over GPUs (the reference folds a pixel's samples in a fixed order,
+ * codelets.cpp:235-306). Consequences for callers: uploaded r,g,b seeds are rounded to multiples of 2^-32, and the sum a work
+ * item collects within one step must stay below 2^31 in magnitude. */
 /* "read_results" (PathTracerApp.cpp:470-475,598-603): the worklist with accumulated r,g,b,
  * sampleCount and pathLength (the two counts wrap at 65536 exactly like the reference's
  * uint16 fields). counters may be NULL. Implies b200pt_sync. */
