@@ -44,3 +44,22 @@ def test_gpu_arm_has_no_cpu_fallback():
         pytest.skip("a GPU is present")
     r = _run(["--steps", "1", "--warmup", "0"])
     assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+
+
+def test_roofline_traffic_is_refused_when_the_capture_is_from_other_sources(monkeypatch):
+    """roofline.traffic comes from a committed ncu capture (ncu cannot run inside the timed region); the capture records the
+    SHA-256 of the NIF kernel's sources and bench.py must answer (None, why) instead of a stale constant when they differ."""
+    sys.path.insert(0, ROOT)
+    import bench
+    value, source = bench.nif_traffic_bytes()
+    if value is not None:                      # a matching capture is committed: it must be the newest round's and sane
+        assert source.startswith("profiles/r") and 1e8 < value < 1e9
+    monkeypatch.setattr(bench, "nif_source_hashes", lambda: {"nif_tc.cu": "edited"})
+    value, why = bench.nif_traffic_bytes()
+    assert value is None and "re-capture" in why
+
+
+def test_multi_gpu_check_is_wired_into_the_gpu_arm():
+    src = open(os.path.join(ROOT, "bench.py")).read()
+    assert 'extras["multi_gpu_check"]' in src and "def multi_gpu_check(" in src and '"bit_equal"' in src and '"counters_equal"' in src
+    assert '"OMP_NUM_THREADS"' in src            # the C++ host run must not inherit torchrun's single-thread setting
